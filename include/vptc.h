@@ -1,0 +1,175 @@
+/* vptc.h — C ABI of libvptcuda: the B200 (sm_100a) drop-in for volume_path_tracer's
+ * per-pixel volumetric path integrator.
+ *
+ * The reference has no FFI layer; its seam is the free function
+ *     void vpt::run(const WorkerParameters&, const Volume&, const Camera&, TileProvider&,
+ *                   Image<float,4>& film, RandomNumberGenerator rng)     include/vpt/worker.hpp:11
+ * called from num_workers jthreads (src/main.cpp:63-87), bracketed by the construction of
+ * VolumeGrids/Volume/Camera/TileProvider/film (src/main.cpp:40-56) and by film_to_image + save
+ * (src/main.cpp:142-143).  Each entry point below names the reference interface it replaces.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function returns 0 on success or
+ * a negative vptc_status, never throws or aborts across the boundary; the message for the last
+ * failure is available from vptc_last_error().  The reference's own convention for the same errors
+ * is `vptFATAL(...)` = message to std::clog + exit(1) (include/vpt/logging.hpp:16); the host `vpt`
+ * CLI maps a non-zero return to exactly that.
+ * A context is driven by one host thread at a time (calls are blocking unless stated).
+ */
+#ifndef VPTC_H
+#define VPTC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VPTC_API __attribute__((visibility("default")))
+
+typedef enum vptc_status {
+    VPTC_OK = 0,
+    VPTC_ERR_INVALID_ARGUMENT = -1,
+    VPTC_ERR_BAD_GRID = -2,      /* buffer is not a float NanoVDB grid of ABI major 32 */
+    VPTC_ERR_CUDA = -3,
+    VPTC_ERR_NO_VOLUME = -4,
+    VPTC_ERR_IO = -5,
+    VPTC_ERR_CONFIG = -6,        /* JSON scene: missing key / wrong type (configuration.cpp:13-19) */
+    VPTC_ERR_UNSUPPORTED = -7
+} vptc_status;
+
+/* ---- Scene POD: vpt::Configuration field for field (include/vpt/configuration.hpp:14-65) ---- */
+typedef struct vptc_camera_parameters { /* configuration.hpp:14-21 */
+    float position[3], look[3], up[3];
+    float vfov_deg, imaging_ratio;
+} vptc_camera_parameters;
+
+typedef struct vptc_infinite_light { float xyz[3]; float multiplier; } vptc_infinite_light; /* :23-26 */
+typedef struct vptc_distant_light {                                                         /* :28-32 */
+    float xyz[3]; float multiplier; float inv_direction[3];
+} vptc_distant_light;
+
+typedef struct vptc_worker_parameters { /* configuration.hpp:34-44 */
+    int32_t single_pixel_enabled;
+    int64_t single_pixel_coord[2];      /* [x, y] */
+    int32_t use_jitter;
+    vptc_infinite_light infinite_light;
+    vptc_distant_light  distant_light;
+    uint32_t max_depth;
+} vptc_worker_parameters;
+
+typedef struct vptc_volume_parameters { /* configuration.hpp:46-53 */
+    float henyey_greenstein_g, le_scale, sigma_a, sigma_s, temperature_offset, temperature_scale;
+} vptc_volume_parameters;
+
+typedef struct vptc_scene { /* configuration.hpp:55-65 (volume_path is returned separately) */
+    uint32_t seed;
+    int64_t  output_size[2];   /* [W, H] */
+    int64_t  tile_size[2];     /* [w, h] */
+    uint32_t num_waves;
+    uint32_t num_workers;      /* mandatory key; used only by CPU baselines */
+    vptc_camera_parameters camera_parameters;
+    vptc_worker_parameters worker_parameters;
+    vptc_volume_parameters volume_parameters;
+} vptc_scene;
+
+/* Work counters of the last render call (the algorithmic-bytes formula
+ * 32*N_rho + 32*N_T + 4*N_maj + 32 per pixel-sample is evaluated from these). */
+typedef struct vptc_counters {
+    uint64_t pixel_samples;    /* camera paths finished                                   */
+    uint64_t density_evals;    /* N_rho: trilinear density evaluations (sampler t < t1)   */
+    uint64_t temperature_evals;/* N_T                                                      */
+    uint64_t majorant_fetches; /* N_maj: update_current_majorant calls (volume.cpp:49,68) */
+    uint64_t rng_draws;
+    uint64_t scatter_events;
+    uint64_t shadow_rays;
+} vptc_counters;
+
+typedef struct vptc_ctx vptc_ctx;
+
+/* ---- context ---- */
+/* Owns all device memory and the render stream of ONE CUDA device (one process per GPU). */
+VPTC_API int  vptc_create(vptc_ctx** out, int device);
+VPTC_API void vptc_destroy(vptc_ctx* ctx);
+/* ctx may be NULL: returns the calling thread's last context-less error. */
+VPTC_API const char* vptc_last_error(const vptc_ctx* ctx);
+
+/* Replaces VolumeGrids(handle) + Volume::Volume (src/volume_grids.cpp:21-33, src/volume.cpp:162-170):
+ * takes the raw serialized NanoVDB grid buffers that nanovdb::io::readGrid returns (density
+ * required, temperature optional: pass NULL/0), applies fix_majorants_for_interpolation
+ * (volume.cpp:104-160) to a private copy — the caller's memory is never mutated and may be freed on
+ * return — bakes the brick-sparse layout and stages it to HBM once. */
+VPTC_API int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_bytes,
+                             const void* temperature_grid, size_t temperature_bytes);
+
+/* Replaces the thread-spawn block + vpt::run (src/main.cpp:63-87, src/worker.cpp:92-208) for waves
+ * first_wave .. first_wave + n_waves - 1 (1-based, tile_provider.cpp:30); job ids are
+ * jid = (wave-1)*ntiles + tile exactly as TileProvider::next() hands them out.  ADDS
+ * (imaging_ratio*L, 1) per pixel-sample into the caller-owned host film, H x W row-major float[4]
+ * (worker.cpp:203-204, image.hpp:59).  Host<->device copies are inside the call. */
+VPTC_API int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves,
+                         float* film_xyzw);
+
+/* Same work, film resident in device memory (d_film_xyzw is a device pointer on ctx's device).
+ * Waves rendered: first_wave + k*wave_stride, k = 0..n_waves-1 (wave_stride >= 1; used to shard a
+ * progressive render across GPUs).  Enqueued on ctx's stream; returns after the kernels finished. */
+VPTC_API int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves,
+                                uint32_t wave_stride, void* d_film_xyzw);
+
+/* Device time (CUDA events on ctx's stream) of the kernels of the last render call, milliseconds. */
+VPTC_API float vptc_last_render_ms(const vptc_ctx* ctx);
+VPTC_API int   vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out);
+/* Counting costs atomics; off by default. */
+VPTC_API int   vptc_enable_counters(vptc_ctx* ctx, int enabled);
+
+/* Parity hook = the reference's single_pixel / Logger<true> debugging aids (worker.cpp:15-49,113-119):
+ * runs the given jobs and returns, per job and per pixel of its tile (row-major inside the tile,
+ * tile_w*tile_h slots per job, unused slots of clipped tiles zero), the un-scaled radiance L (XYZ)
+ * and the number of RNG draws the job had consumed when the pixel finished. */
+VPTC_API int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint64_t* jids, size_t n_jobs,
+                             float* per_pixel_xyz, uint32_t* per_pixel_ndraws);
+
+/* Parity hook = Volume::log_majorant_trace (volume.cpp:176-192): merged majorant segments
+ * {t0, t1, d_maj} (index-space t) of n world-space rays; at most max_segs per ray are stored,
+ * n_segs[i] receives the true count. */
+VPTC_API int vptc_trace_segments(vptc_ctx* ctx, const float* origins_xyz, const float* dirs_xyz, size_t n_rays,
+                                 uint32_t max_segs, float* segs_t0_t1_dmaj, uint32_t* n_segs);
+
+/* Parity hook for the trilinear sampler (SampleFromVoxels<Acc,1>): grid 0 = density, 1 = temperature;
+ * index-space positions. Also returns getDim/majorant per position when the pointers are non-NULL. */
+VPTC_API int vptc_sample_grid(vptc_ctx* ctx, int grid, const float* index_xyz, size_t n, float* values,
+                              uint32_t* dims, float* majorants);
+
+/* Replaces film_to_image (src/main.cpp:12-24, include/vpt/color.hpp:8-30): XYZ/N -> linear sRGB ->
+ * sRGB OETF -> clamp -> *255 -> truncate, on the device. Host film in, host RGB8 out. */
+VPTC_API int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8);
+
+/* ---- host-side helpers (no GPU needed) ---- */
+/* Replaces read_configuration (src/configuration.cpp:8-22): all keys mandatory. volume_path is
+ * copied (relative, as written in the file) into volume_path_out. */
+VPTC_API int vptc_scene_from_json_file(const char* path, vptc_scene* out, char* volume_path_out, size_t volume_path_cap);
+VPTC_API int vptc_scene_from_json(const char* json_text, vptc_scene* out, char* volume_path_out, size_t volume_path_cap);
+
+/* Replaces nanovdb::io::readGrid(path, name) as used by src/volume_grids.cpp:39-67. On success *grid is
+ * malloc'ed (release with vptc_free). A missing grid name returns VPTC_ERR_BAD_GRID. */
+VPTC_API int  vptc_nvdb_read_grid(const char* path, const char* grid_name, void** grid, size_t* bytes);
+VPTC_API int  vptc_nvdb_write_grids(const char* path, const void* const* grids, size_t n_grids);
+VPTC_API void vptc_free(void* p);
+
+/* Synthetic procedural volumes (BASELINE.json configs), returned as serialized NanoVDB float grids.
+ * kind: "fire" (density+temperature), "cloud" (WDAS-shaped sparse density), "dense" (all-leaf noise),
+ *       "torus" (fog torus), "tiles" (test volume with active tiles at every tree level).
+ * dims = index-space extent; voxel_size/seed as named; anchor_xyz (NULL = world origin) = world position
+ * of the box centre (centre of the base for "fire"). temperature may be NULL. */
+VPTC_API int vptc_synth_volume(const char* kind, const int32_t dims[3], double voxel_size, uint32_t seed, const double* anchor_xyz,
+                               void** density, size_t* density_bytes, void** temperature, size_t* temperature_bytes);
+
+/* 8-bit RGB PNG (replaces Image<uchar,3>::save, src/image_io.cpp:18-58). */
+VPTC_API int vptc_write_png(const char* path, const uint8_t* rgb8, int64_t width, int64_t height);
+
+VPTC_API const char* vptc_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VPTC_H */

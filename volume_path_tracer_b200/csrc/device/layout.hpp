@@ -1,0 +1,75 @@
+// layout.hpp — the brick-sparse HBM layout a NanoVDB float grid is baked into (shared host/device).
+//
+// What it must reproduce, and how:
+//   getValue(ijk)  (NV/NanoVDB.h GetValue)      cells -> lower slots -> 9^3 apron bricks / tile values
+//   getDim(ijk)    (NV/NanoVDB.h:3071-3083,3564-3577) ONE load: the 128^3-cell entry carries the dim code
+//   majorant(ijk)  (src/volume.cpp:18-36)        lower-slot entry carries the patched leaf maximum
+//
+// Level 0 "cells": a DENSE 3-D array of 128^3-voxel cells over the span of the grid's root entries
+//   (root keys = ijk >> 12; each root entry = 32^3 cells). The sparse root table and the 32^3 upper
+//   tables of NanoVDB collapse into this one array (1 MB for a 2k^3 cloud), so a lookup is
+//   cell -> lower slot -> voxel: two dependent 4/8-byte loads before the voxel data instead of three
+//   pointer hops plus a linear root search.
+// Level 1 "lower slots": per lower node 16^3 entries of 8 bytes {code, majorant}.
+// Level 2 "bricks": per leaf 9x9x9 floats = the 8^3 voxels plus a +1 apron in x, y, z (values read
+//   through getValue at bake time, so whatever lies beyond the leaf — another leaf, a tile, background —
+//   is already folded in). A trilinear stencil whose base voxel lies in a leaf touches exactly one brick.
+//   Brick stride is padded to 736 floats (2944 B = 92 sectors of 32 B).
+#pragma once
+#include <cstdint>
+
+namespace vptd {
+
+constexpr uint32_t CELL_KIND_TILE = 0x80000000u;  // else: lower-node index
+constexpr uint32_t CELL_DIM_SHIFT = 28;           // 2 bits: 0 -> 8, 1 -> 128, 2 -> 4096
+constexpr uint32_t CELL_DIM_MASK = 0x30000000u;
+constexpr uint32_t CELL_INDEX_MASK = 0x0fffffffu;
+constexpr uint32_t SLOT_KIND_TILE = 0x80000000u;  // else: brick index
+constexpr uint32_t SLOT_INDEX_MASK = 0x7fffffffu;
+
+struct Slot { uint32_t code; float majorant; }; // 8 bytes, loaded as one 64-bit word
+
+constexpr int BRICK_EDGE = 9;
+constexpr int BRICK_STRIDE = 736; // floats; >= 9^3 = 729
+
+struct GridDev {
+    // NanoVDB Map, float members verbatim (NV/NanoVDB.h:1375-1381)
+    float mat[9], invMat[9], vec[3];
+    int32_t bbox_min[3], bbox_max[3]; // indexBBox(): AABB of active values, inclusive
+    int32_t cell_org[3];              // index-space origin of cell (0,0,0): multiple of 4096
+    int32_t cell_dim[3];              // number of 128^3 cells per axis (multiple of 32)
+    uint32_t background_tile;         // tile index of {background, inactive}: always 0
+    const uint32_t* cells;            // [cell_dim x*y*z]
+    const Slot* slots;                // [nLower * 4096]
+    const float* tile_value;          // [nTiles] value getValue returns inside the tile
+    const float* tile_majorant;       // [nTiles] active ? value : 0        (volume.cpp:28-34)
+    const float* bricks;              // [nBricks * BRICK_STRIDE]
+    uint32_t n_lower, n_bricks, n_tiles, pad_;
+};
+
+// vpt::Configuration flattened to what the kernels read, plus host-precomputed constants.
+struct SceneDev {
+    // camera (src/camera.cpp:45-57): raster -> world direction affine, row-major linear + translation
+    float cam_m[9], cam_t[3], cam_pos[3];
+    float imaging_ratio;
+    // lights
+    float inf_light[3];      // infinite_light.xyz * multiplier         (worker.cpp:199)
+    float dist_Li[3];        // distant_light.xyz * multiplier          (worker.cpp:55)
+    float dist_wi[3];        // distant_light.inv_direction.normalized() (worker.cpp:54)
+    int32_t dist_light_on;   // Li != 0                                  (worker.cpp:57)
+    // volume parameters
+    float sigma_a, sigma_s, sigma_t, g, le_scale, temperature_offset, temperature_scale;
+    uint32_t max_depth;
+    int32_t use_jitter, has_temperature;
+    int32_t single_pixel_enabled; int64_t single_pixel_x, single_pixel_y;
+    // tiling (src/tile_provider.cpp:14-31,95-105)
+    int64_t W, H, tw, th, ntx, nty;
+    uint64_t ntiles;
+    uint32_t seed;
+};
+
+struct CountersDev {
+    unsigned long long pixel_samples, density_evals, temperature_evals, majorant_fetches, rng_draws, scatter_events, shadow_rays;
+};
+
+} // namespace vptd

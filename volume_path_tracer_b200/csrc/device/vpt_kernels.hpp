@@ -1,0 +1,36 @@
+// vpt_kernels.hpp — host-visible interface of vpt_kernels.cu.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "layout.hpp"
+
+#ifndef VPT_BLOCK_THREADS
+#define VPT_BLOCK_THREADS 128
+#endif
+
+namespace vptd {
+
+struct RenderArgs {
+    GridDev density, temperature;
+    SceneDev scene;
+    const float* bb_table;        // 1500 floats: precompute_blackbody.cpp's bb_xyz[500]
+    float* film;                  // H*W*4, accumulated into (render mode)
+    unsigned long long* queue;    // device job counter, zeroed before launch
+    unsigned long long n_jobs;    // ntiles * n_waves (render) or number of listed jobs (trace)
+    uint32_t first_wave, wave_stride;
+    const uint64_t* trace_jids;   // trace mode
+    float* trace_xyz;
+    uint32_t* trace_ndraws;
+    CountersDev* counters;        // COUNT builds
+};
+
+cudaError_t upload_cie_table(const float* cie471x3);
+cudaError_t launch_render(const RenderArgs& args, bool trace, bool count, int grid_blocks, cudaStream_t stream);
+int render_blocks_per_sm(bool trace, bool count);
+cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
+cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);
+cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);
+
+} // namespace vptd

@@ -1,0 +1,211 @@
+// bake.cpp — NanoVDB float grid -> brick-sparse device layout (device/layout.hpp), incl. the one-time
+// halo-majorant patch. Replaces Volume::Volume / fix_majorants_for_interpolation (src/volume.cpp:104-170):
+// the reference mutates leaf.mMaximum inside the caller's grid buffer; we leave the caller's buffer
+// untouched and write the patched maxima into the baked lower-slot table.
+#include "bake.hpp"
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <thread>
+
+#include "nvdb_build.hpp" // check_grid
+#include "nvdb_format.h"
+
+namespace vpt_host {
+using namespace nvdbf;
+using namespace vptd;
+
+namespace {
+
+// Stateless top-down value lookup on the serialized tree (what ReadAccessor::getValue returns:
+// the leaf voxel, else the tile value of the slot where the descent ends, else the background).
+struct TreeView {
+    const GridData* grid; const TreeData* tree; const RootData* root; const RootTile* tiles;
+    const UpperData* upper0; const LowerData* lower0; const LeafData* leaf0;
+    explicit TreeView(const void* data)
+    {
+        grid = static_cast<const GridData*>(data);
+        tree = tree_of(grid); root = root_of(grid); tiles = root_tiles(root);
+        const char* t = reinterpret_cast<const char*>(tree);
+        leaf0 = reinterpret_cast<const LeafData*>(t + tree->nodeOffset[0]);
+        lower0 = reinterpret_cast<const LowerData*>(t + tree->nodeOffset[1]);
+        upper0 = reinterpret_cast<const UpperData*>(t + tree->nodeOffset[2]);
+    }
+    const UpperData* upper_of(const RootTile& rt) const { return reinterpret_cast<const UpperData*>(reinterpret_cast<const char*>(root) + rt.child); }
+    const LowerData* lower_of(const UpperData* u, uint32_t n) const { return reinterpret_cast<const LowerData*>(reinterpret_cast<const char*>(u) + u->table[n].child); }
+    const LeafData* leaf_of(const LowerData* l, uint32_t n) const { return reinterpret_cast<const LeafData*>(reinterpret_cast<const char*>(l) + l->table[n].child); }
+    float value(int32_t x, int32_t y, int32_t z) const
+    {
+        const uint64_t key = root_key(x, y, z);
+        const RootTile* rt = nullptr;
+        for (uint32_t i = 0; i < root->tableSize; ++i) if (tiles[i].key == key) { rt = &tiles[i]; break; }
+        if (!rt) return root->background;
+        if (rt->child == 0) return rt->value;
+        const UpperData* u = upper_of(*rt);
+        const uint32_t un = upper_offset(x, y, z);
+        if (!mask_on(u->childMask, un)) return u->table[un].value;
+        const LowerData* l = lower_of(u, un);
+        const uint32_t ln = lower_offset(x, y, z);
+        if (!mask_on(l->childMask, ln)) return l->table[ln].value;
+        return leaf_of(l, ln)->values[leaf_offset(x, y, z)];
+    }
+};
+
+template <class F>
+void parallel_for(size_t n, F&& f)
+{
+    unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
+    if (n < 256) nt = 1;
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const size_t b = next.fetch_add(64);
+            if (b >= n) break;
+            for (size_t i = b; i < std::min(n, b + 64); ++i) f(i);
+        }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; ++t) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+}
+
+} // namespace
+
+void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& out)
+{
+    if (const char* bad = check_grid(data, bytes)) throw std::runtime_error(bad);
+    const TreeView tv(data);
+    const GridData* g = tv.grid;
+    const size_t nUpper = tv.tree->nodeCount[2], nLower = tv.tree->nodeCount[1], nLeaf = tv.tree->nodeCount[0];
+
+    GridDev& h = out.header;
+    std::memset(&h, 0, sizeof(h));
+    std::memcpy(h.mat, g->map.matF, sizeof(h.mat));
+    std::memcpy(h.invMat, g->map.invMatF, sizeof(h.invMat));
+    std::memcpy(h.vec, g->map.vecF, sizeof(h.vec));
+    for (int a = 0; a < 3; ++a) { h.bbox_min[a] = tv.root->bbox[a]; h.bbox_max[a] = tv.root->bbox[3 + a]; }
+
+    // ---- tiles: index 0 = {background, inactive} ----
+    out.tile_value.assign(1, tv.root->background);
+    out.tile_majorant.assign(1, 0.0f);
+    std::map<std::pair<uint32_t, bool>, uint32_t> tileIndex; // (value bits, active) -> index
+    auto tile_of = [&](float v, bool active) -> uint32_t {
+        uint32_t bits; std::memcpy(&bits, &v, 4);
+        if (!active && v == tv.root->background) { uint32_t bb; std::memcpy(&bb, &tv.root->background, 4); if (bb == bits) return 0u; }
+        auto key = std::make_pair(bits, active);
+        auto it = tileIndex.find(key);
+        if (it != tileIndex.end()) return it->second;
+        const uint32_t idx = uint32_t(out.tile_value.size());
+        if (idx > CELL_INDEX_MASK) throw std::runtime_error("bake: too many distinct tile values");
+        out.tile_value.push_back(v);
+        out.tile_majorant.push_back(active ? v : 0.0f); // probeValue(ijk, v) ? v : 0   (volume.cpp:28-34)
+        tileIndex.emplace(key, idx);
+        return idx;
+    };
+
+    // ---- cells: dense over the span of the root keys ----
+    int32_t kmin[3] = {0, 0, 0}, kmax[3] = {0, 0, 0};
+    for (uint32_t i = 0; i < tv.root->tableSize; ++i) {
+        int32_t o[3]; root_key_origin(tv.tiles[i].key, o);
+        for (int a = 0; a < 3; ++a) {
+            const int32_t k = o[a] >> 12;
+            if (i == 0) { kmin[a] = kmax[a] = k; } else { kmin[a] = std::min(kmin[a], k); kmax[a] = std::max(kmax[a], k); }
+        }
+    }
+    uint64_t nRootCells = 1;
+    for (int a = 0; a < 3; ++a) {
+        h.cell_org[a] = kmin[a] * 4096;
+        h.cell_dim[a] = (kmax[a] - kmin[a] + 1) * 32;
+        nRootCells *= uint64_t(kmax[a] - kmin[a] + 1);
+    }
+    if (nRootCells > 4096) throw std::runtime_error("bake: grid spans more than 4096 root entries (index extent too large for the dense cell table)");
+    const uint32_t NONE = CELL_KIND_TILE | (2u << CELL_DIM_SHIFT) | 0u; // background, dim 4096 (NanoVDB.h:3081)
+    out.cells.assign(size_t(nRootCells) * 32768, NONE);
+    auto cell_at = [&](int32_t x, int32_t y, int32_t z) -> uint32_t& {
+        const size_t cx = size_t((x - h.cell_org[0]) >> 7), cy = size_t((y - h.cell_org[1]) >> 7), cz = size_t((z - h.cell_org[2]) >> 7);
+        return out.cells[(cx * size_t(h.cell_dim[1]) + cy) * size_t(h.cell_dim[2]) + cz];
+    };
+    if (nLower > CELL_INDEX_MASK || nLeaf > SLOT_INDEX_MASK) throw std::runtime_error("bake: too many nodes");
+    (void)nUpper;
+    for (uint32_t i = 0; i < tv.root->tableSize; ++i) {
+        const RootTile& rt = tv.tiles[i];
+        int32_t o[3]; root_key_origin(rt.key, o);
+        if (rt.child == 0) { // constant root tile: dim 4096 (NanoVDB.h:3079)
+            const uint32_t code = CELL_KIND_TILE | (2u << CELL_DIM_SHIFT) | tile_of(rt.value, rt.state > 0u);
+            for (int a = 0; a < 32; ++a) for (int b = 0; b < 32; ++b) for (int c = 0; c < 32; ++c) cell_at(o[0] + 128 * a, o[1] + 128 * b, o[2] + 128 * c) = code;
+            continue;
+        }
+        const UpperData* u = tv.upper_of(rt);
+        const bool uSkip = (u->flags & 1u) != 0; // node without active values: getDim returns its own dim (NanoVDB.h:3567-3568)
+        for (uint32_t n = 0; n < 32768; ++n) {
+            const int32_t x = o[0] + int32_t(n >> 10) * 128, y = o[1] + int32_t((n >> 5) & 31) * 128, z = o[2] + int32_t(n & 31) * 128;
+            uint32_t code;
+            if (mask_on(u->childMask, n)) {
+                const LowerData* l = tv.lower_of(u, n);
+                const uint32_t li = uint32_t(l - tv.lower0);
+                const uint32_t dimc = uSkip ? 2u : ((l->flags & 1u) ? 1u : 0u);
+                code = (dimc << CELL_DIM_SHIFT) | li;
+            } else {
+                code = CELL_KIND_TILE | ((uSkip ? 2u : 1u) << CELL_DIM_SHIFT) | tile_of(u->table[n].value, mask_on(u->valueMask, n));
+            }
+            cell_at(x, y, z) = code;
+        }
+    }
+
+    // ---- lower slots (codes now, majorants after the patch) ----
+    out.slots.assign(nLower * 4096 * 2, 0u);
+    for (size_t li = 0; li < nLower; ++li) {
+        const LowerData* l = tv.lower0 + li;
+        for (uint32_t n = 0; n < 4096; ++n) {
+            uint32_t code; float maj;
+            if (mask_on(l->childMask, n)) {
+                const LeafData* lf = tv.leaf_of(l, n);
+                code = uint32_t(lf - tv.leaf0);
+                maj = lf->maximum; // patched below
+            } else {
+                const uint32_t ti = tile_of(l->table[n].value, mask_on(l->valueMask, n));
+                code = SLOT_KIND_TILE | ti;
+                maj = out.tile_majorant[ti];
+            }
+            out.slots[(li * 4096 + n) * 2] = code;
+            std::memcpy(&out.slots[(li * 4096 + n) * 2 + 1], &maj, 4);
+        }
+    }
+
+    // ---- bricks with +1 apron, and patched maxima ----
+    out.bricks.assign(nLeaf * size_t(BRICK_STRIDE), 0.0f);
+    out.brick_max.assign(nLeaf, 0.0f);
+    parallel_for(nLeaf, [&](size_t bi) {
+        const LeafData* lf = tv.leaf0 + bi;
+        const int32_t o[3] = {lf->bboxMin[0] & ~7, lf->bboxMin[1] & ~7, lf->bboxMin[2] & ~7};
+        float* dst = &out.bricks[bi * size_t(BRICK_STRIDE)];
+        for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) for (int k = 0; k < 9; ++k) {
+            const bool core = i < 8 && j < 8 && k < 8;
+            dst[(i * 9 + j) * 9 + k] = core ? lf->values[(i << 6) | (j << 3) | k] : tv.value(o[0] + i, o[1] + j, o[2] + k);
+        }
+        float m = lf->maximum; // stats over ACTIVE voxels only (NV/tools/GridStats.h:716-730)
+        if (patch_majorants) {
+            // max over the 1-voxel shell [o-1, o+8]^3 \ leaf, read through getValue (volume.cpp:128-156)
+            for (int i = -1; i <= 8; ++i) for (int j = -1; j <= 8; ++j) for (int k = -1; k <= 8; ++k) {
+                if (i >= 0 && i < 8 && j >= 0 && j < 8 && k >= 0 && k < 8) continue;
+                float v;
+                if (i >= 0 && j >= 0 && k >= 0) v = dst[(i * 9 + j) * 9 + k]; // already fetched for the apron
+                else v = tv.value(o[0] + i, o[1] + j, o[2] + k);
+                m = std::max(m, v);
+            }
+        }
+        out.brick_max[bi] = m;
+    });
+    for (size_t e = 0; e < nLower * 4096; ++e) {
+        const uint32_t code = out.slots[e * 2];
+        if (!(code & SLOT_KIND_TILE)) std::memcpy(&out.slots[e * 2 + 1], &out.brick_max[code], 4);
+    }
+    h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
+    h.background_tile = 0;
+}
+
+} // namespace vpt_host

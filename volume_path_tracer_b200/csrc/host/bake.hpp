@@ -1,0 +1,25 @@
+// bake.hpp — host-side result of baking a NanoVDB float grid into the device layout (device/layout.hpp).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "../device/layout.hpp"
+
+namespace vpt_host {
+
+struct BakedGrid {
+    vptd::GridDev header;             // pointers left null; filled by the uploader
+    std::vector<uint32_t> cells;
+    std::vector<uint32_t> slots;      // 2 x uint32 per slot: {code, majorant bits}
+    std::vector<float> tile_value, tile_majorant;
+    std::vector<float> bricks;        // n_bricks * BRICK_STRIDE
+    std::vector<float> brick_max;     // patched leaf maxima, leaf-array order (also folded into `slots`)
+    size_t device_bytes() const { return cells.size() * 4 + slots.size() * 4 + (tile_value.size() + tile_majorant.size() + bricks.size()) * 4; }
+};
+
+// Throws std::runtime_error on a malformed grid. patch_majorants = apply fix_majorants_for_interpolation
+// (density grid: yes; temperature grid: maxima unused).
+void bake_grid(const void* grid, size_t bytes, bool patch_majorants, BakedGrid& out);
+
+} // namespace vpt_host

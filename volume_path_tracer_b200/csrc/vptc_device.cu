@@ -1,0 +1,369 @@
+// vptc_device.cu — the device-facing entry points of include/vptc.h: context, volume staging, render,
+// parity hooks. Plain CUDA runtime; no torch types cross this boundary.
+#include <algorithm>
+#include <cstring>
+#include <exception>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "device/vpt_kernels.hpp"
+#include "host/bake.hpp"
+#include "host/scene_prep.hpp"
+#include "vptc.h"
+#include "vptc_internal.hpp"
+
+using namespace vptd;
+
+struct DeviceGrid {
+    GridDev dev{};
+    void *cells = nullptr, *slots = nullptr, *tile_value = nullptr, *tile_majorant = nullptr, *bricks = nullptr;
+    size_t bytes = 0;
+    void release()
+    {
+        cudaFree(cells); cudaFree(slots); cudaFree(tile_value); cudaFree(tile_majorant); cudaFree(bricks);
+        cells = slots = tile_value = tile_majorant = bricks = nullptr; bytes = 0;
+    }
+};
+
+struct vptc_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string error;
+    DeviceGrid density, temperature;
+    bool has_volume = false, has_temperature = false;
+    float* bb_table = nullptr;
+    unsigned long long* queue = nullptr;
+    CountersDev* counters = nullptr;
+    bool count = false;
+    float last_ms = 0.0f;
+    vptc_counters last_counters{};
+    int num_sms = 0;
+    // scratch film for the host-buffer path
+    float* film = nullptr; size_t film_floats = 0;
+    float* pinned = nullptr; size_t pinned_floats = 0;
+};
+
+namespace {
+
+int fail(vptc_ctx* c, int code, const std::string& msg)
+{
+    if (c) c->error = msg;
+    vptc_internal::set_global_error(msg);
+    return code;
+}
+#define CU(call)                                                                                                   \
+    do {                                                                                                           \
+        cudaError_t e_ = (call);                                                                                   \
+        if (e_ != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
+{
+    g.release();
+    g.dev = b.header;
+    auto up = [&](void** dst, const void* src, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, bytes ? bytes : 16);
+        if (e != cudaSuccess) return e;
+        g.bytes += bytes;
+        return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
+    };
+    CU(up(&g.cells, b.cells.data(), b.cells.size() * 4));
+    CU(up(&g.slots, b.slots.data(), b.slots.size() * 4));
+    CU(up(&g.tile_value, b.tile_value.data(), b.tile_value.size() * 4));
+    CU(up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4));
+    CU(up(&g.bricks, b.bricks.data(), b.bricks.size() * 4));
+    CU(cudaStreamSynchronize(ctx->stream));
+    g.dev.cells = static_cast<const uint32_t*>(g.cells);
+    g.dev.slots = static_cast<const Slot*>(g.slots);
+    g.dev.tile_value = static_cast<const float*>(g.tile_value);
+    g.dev.tile_majorant = static_cast<const float*>(g.tile_majorant);
+    g.dev.bricks = static_cast<const float*>(g.bricks);
+    return VPTC_OK;
+}
+
+int check_scene(vptc_ctx* ctx, const vptc_scene* s)
+{
+    if (!s) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "scene is null");
+    if (s->output_size[0] <= 0 || s->output_size[1] <= 0 || s->tile_size[0] <= 0 || s->tile_size[1] <= 0)
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "output_size and tile_size must be positive");
+    if (s->tile_size[0] * s->tile_size[1] > (int64_t(1) << 20)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile too large");
+    return VPTC_OK;
+}
+
+// Launch the megakernel over n_jobs jobs and wait; fills last_ms / counters.
+int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace)
+{
+    vpt_host::prepare_scene(*scene, ctx->has_temperature, A.scene);
+    A.density = ctx->density.dev;
+    A.temperature = ctx->has_temperature ? ctx->temperature.dev : ctx->density.dev;
+    A.bb_table = ctx->bb_table;
+    A.queue = ctx->queue;
+    A.counters = ctx->counters;
+    CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
+    if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
+    const int per_sm = render_blocks_per_sm(trace, ctx->count);
+    if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
+    // persistent grid: every SM filled to its occupancy limit, never more blocks than jobs need
+    unsigned long long want = (A.n_jobs + VPT_BLOCK_THREADS - 1) / VPT_BLOCK_THREADS;
+    int blocks = int(std::min<unsigned long long>(want ? want : 1ULL, (unsigned long long)(ctx->num_sms) * per_sm));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    CU(launch_render(A, trace, ctx->count, blocks, ctx->stream));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    CU(cudaEventSynchronize(ctx->ev1));
+    CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
+    if (ctx->count) {
+        CountersDev h;
+        CU(cudaMemcpy(&h, ctx->counters, sizeof(h), cudaMemcpyDeviceToHost));
+        ctx->last_counters = {h.pixel_samples, h.density_evals, h.temperature_evals, h.majorant_fetches, h.rng_draws, h.scatter_events, h.shadow_rays};
+    }
+    return VPTC_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* vptc_last_error(const vptc_ctx* ctx) { return ctx ? ctx->error.c_str() : vptc_internal::global_error(); }
+
+int vptc_create(vptc_ctx** out, int device)
+{
+    vptc_ctx* ctx = nullptr;
+    if (!out) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_create: out is null");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, VPTC_ERR_CUDA, std::string("no CUDA device available (") + cudaGetErrorString(e) + "); this library has no CPU fallback");
+    if (device < 0 || device >= n) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_create: device index out of range");
+    std::unique_ptr<vptc_ctx> c(new vptc_ctx);
+    ctx = c.get();
+    ctx->device = device;
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    ctx->num_sms = prop.multiProcessorCount;
+    CU(cudaStreamCreate(&ctx->stream)); // blocking stream: ordered after work on the legacy default stream (torch)
+    CU(cudaEventCreate(&ctx->ev0));
+    CU(cudaEventCreate(&ctx->ev1));
+    CU(cudaMalloc(&ctx->bb_table, 1500 * sizeof(float)));
+    CU(cudaMalloc(&ctx->queue, sizeof(unsigned long long)));
+    CU(cudaMalloc(&ctx->counters, sizeof(CountersDev)));
+    std::vector<float> bb(1500);
+    vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
+    CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
+    CU(upload_cie_table(vpt_host::cie_table()));
+    *out = c.release();
+    return VPTC_OK;
+}
+
+void vptc_destroy(vptc_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    ctx->density.release(); ctx->temperature.release();
+    cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_bytes, const void* temperature_grid, size_t temperature_bytes)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: ctx is null");
+    if (!density_grid) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: the density grid is required (volume_grids.cpp:48-56)");
+    CU(cudaSetDevice(ctx->device));
+    try {
+        vpt_host::BakedGrid b;
+        vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
+        int rc = upload(ctx, b, ctx->density);
+        if (rc != VPTC_OK) return rc;
+        ctx->has_temperature = false;
+        ctx->temperature.release();
+        if (temperature_grid && temperature_bytes) {
+            vpt_host::BakedGrid t;
+            vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t);
+            rc = upload(ctx, t, ctx->temperature);
+            if (rc != VPTC_OK) return rc;
+            ctx->has_temperature = true;
+        }
+    } catch (const std::exception& e) {
+        return fail(ctx, VPTC_ERR_BAD_GRID, std::string("vptc_set_volume: ") + e.what());
+    }
+    ctx->has_volume = true;
+    return VPTC_OK;
+}
+
+int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, uint32_t wave_stride, void* d_film)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (!d_film || first_wave < 1 || wave_stride < 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device: film null, first_wave < 1 or wave_stride < 1");
+    CU(cudaSetDevice(ctx->device));
+    ctx->last_ms = 0.0f;
+    if (n_waves == 0) return VPTC_OK;
+    RenderArgs A{};
+    A.film = static_cast<float*>(d_film);
+    A.first_wave = first_wave; A.wave_stride = wave_stride;
+    vptd::SceneDev tmp; vpt_host::prepare_scene(*scene, ctx->has_temperature, tmp);
+    A.n_jobs = tmp.ntiles * (unsigned long long)n_waves;
+    return run_render(ctx, scene, A, /*trace=*/false);
+}
+
+int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render: ctx is null");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (!film_xyzw) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render: film is null");
+    CU(cudaSetDevice(ctx->device));
+    const size_t n = size_t(scene->output_size[0]) * size_t(scene->output_size[1]) * 4;
+    if (ctx->film_floats < n) {
+        cudaFree(ctx->film); ctx->film = nullptr; ctx->film_floats = 0;
+        CU(cudaMalloc(&ctx->film, n * sizeof(float)));
+        ctx->film_floats = n;
+    }
+    if (ctx->pinned_floats < n) {
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr; ctx->pinned_floats = 0;
+        CU(cudaMallocHost(&ctx->pinned, n * sizeof(float)));
+        ctx->pinned_floats = n;
+    }
+    // The device renders this call's waves into a zeroed film; the host then ADDS it into the caller's
+    // film, which keeps the reference's "film accumulates" contract without uploading the old film.
+    CU(cudaMemsetAsync(ctx->film, 0, n * sizeof(float), ctx->stream));
+    const int rc = vptc_render_device(ctx, scene, first_wave, n_waves, 1, ctx->film);
+    if (rc != VPTC_OK) return rc;
+    CU(cudaMemcpyAsync(ctx->pinned, ctx->film, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; ++i) film_xyzw[i] += ctx->pinned[i];
+    return VPTC_OK;
+}
+
+float vptc_last_render_ms(const vptc_ctx* ctx) { return ctx ? ctx->last_ms : 0.0f; }
+
+int vptc_enable_counters(vptc_ctx* ctx, int enabled)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_enable_counters: ctx is null");
+    ctx->count = enabled != 0;
+    return VPTC_OK;
+}
+int vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out)
+{
+    if (!ctx || !out) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_get_counters: null argument");
+    *out = ctx->last_counters;
+    return VPTC_OK;
+}
+
+int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint64_t* jids, size_t n_jobs, float* per_pixel_xyz, uint32_t* per_pixel_ndraws)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_jobs: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (!jids || !per_pixel_xyz || !per_pixel_ndraws) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_jobs: null argument");
+    if (n_jobs == 0) return VPTC_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t slots = size_t(scene->tile_size[0]) * size_t(scene->tile_size[1]) * n_jobs;
+    uint64_t* d_jids = nullptr; float* d_xyz = nullptr; uint32_t* d_nd = nullptr;
+    auto cleanup = [&]() { cudaFree(d_jids); cudaFree(d_xyz); cudaFree(d_nd); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_jids, n_jobs * 8)) != cudaSuccess || (e = cudaMalloc(&d_xyz, slots * 12)) != cudaSuccess || (e = cudaMalloc(&d_nd, slots * 4)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_jobs: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_jids, jids, n_jobs * 8, cudaMemcpyHostToDevice, ctx->stream);
+    cudaMemsetAsync(d_xyz, 0, slots * 12, ctx->stream);
+    cudaMemsetAsync(d_nd, 0, slots * 4, ctx->stream);
+    RenderArgs A{};
+    A.n_jobs = n_jobs; A.first_wave = 1; A.wave_stride = 1;
+    A.trace_jids = d_jids; A.trace_xyz = d_xyz; A.trace_ndraws = d_nd;
+    int rc = run_render(ctx, scene, A, /*trace=*/true);
+    if (rc == VPTC_OK) {
+        e = cudaMemcpy(per_pixel_xyz, d_xyz, slots * 12, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(per_pixel_ndraws, d_nd, slots * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_jobs: copy back: ") + cudaGetErrorString(e));
+    }
+    cleanup();
+    return rc;
+}
+
+int vptc_trace_segments(vptc_ctx* ctx, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_segments: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (!origins || !dirs || !segs || !n_segs || max_segs == 0) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_segments: bad argument");
+    if (n == 0) return VPTC_OK;
+    CU(cudaSetDevice(ctx->device));
+    float *d_o = nullptr, *d_d = nullptr, *d_s = nullptr; uint32_t* d_n = nullptr;
+    auto cleanup = [&]() { cudaFree(d_o); cudaFree(d_d); cudaFree(d_s); cudaFree(d_n); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_o, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_d, n * 12)) != cudaSuccess ||
+        (e = cudaMalloc(&d_s, n * size_t(max_segs) * 12)) != cudaSuccess || (e = cudaMalloc(&d_n, n * 4)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_segments: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_o, origins, n * 12, cudaMemcpyHostToDevice, ctx->stream);
+    cudaMemcpyAsync(d_d, dirs, n * 12, cudaMemcpyHostToDevice, ctx->stream);
+    cudaMemsetAsync(d_s, 0, n * size_t(max_segs) * 12, ctx->stream);
+    e = launch_segments(ctx->density.dev, d_o, d_d, n, max_segs, d_s, d_n, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(segs, d_s, n * size_t(max_segs) * 12, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(n_segs, d_n, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_segments: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+int vptc_sample_grid(vptc_ctx* ctx, int grid, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_sample_grid: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (grid != 0 && grid != 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_sample_grid: grid must be 0 (density) or 1 (temperature)");
+    if (grid == 1 && !ctx->has_temperature) return fail(ctx, VPTC_ERR_NO_VOLUME, "vptc_sample_grid: no temperature grid");
+    if (!xyz) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_sample_grid: xyz is null");
+    if (n == 0) return VPTC_OK;
+    CU(cudaSetDevice(ctx->device));
+    float *d_p = nullptr, *d_v = nullptr, *d_m = nullptr; uint32_t* d_d = nullptr;
+    auto cleanup = [&]() { cudaFree(d_p); cudaFree(d_v); cudaFree(d_m); cudaFree(d_d); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_p, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_v, n * 4)) != cudaSuccess || (e = cudaMalloc(&d_m, n * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&d_d, n * 4)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_sample_grid: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_p, xyz, n * 12, cudaMemcpyHostToDevice, ctx->stream);
+    const GridDev& G = grid == 1 ? ctx->temperature.dev : ctx->density.dev;
+    e = launch_sample(G, d_p, n, d_v, d_d, d_m, ctx->stream);
+    if (e == cudaSuccess && values) e = cudaMemcpyAsync(values, d_v, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && dims) e = cudaMemcpyAsync(dims, d_d, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && majorants) e = cudaMemcpyAsync(majorants, d_m, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_sample_grid: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image: ctx is null");
+    if (!film_xyzw || !rgb8 || width <= 0 || height <= 0) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    const size_t n = size_t(width) * size_t(height);
+    float* d_f = nullptr; uint8_t* d_rgb = nullptr;
+    auto cleanup = [&]() { cudaFree(d_f); cudaFree(d_rgb); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_f, n * 16)) != cudaSuccess || (e = cudaMalloc(&d_rgb, n * 3)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    e = cudaMemcpyAsync(d_f, film_xyzw, n * 16, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_resolve(d_f, n, d_rgb, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb8, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+} // extern "C"

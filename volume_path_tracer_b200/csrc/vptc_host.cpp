@@ -1,0 +1,112 @@
+// vptc_host.cpp — the host-only entry points of include/vptc.h (no CUDA calls here):
+// .nvdb I/O, synthetic volumes, scene JSON, PNG. The device side lives in vptc_device.cu.
+#include <cstdlib>
+#include <cstring>
+#include <exception>
+#include <string>
+
+#include "host/json_scene.hpp"
+#include "host/nvdb_build.hpp"
+#include "host/nvdb_io.hpp"
+#include "host/png_write.hpp"
+#include "host/synth.hpp"
+#include "vptc.h"
+#include "vptc_internal.hpp"
+
+namespace vptc_internal {
+static thread_local std::string g_tls_error;
+void set_global_error(const std::string& msg) { g_tls_error = msg; }
+const char* global_error() { return g_tls_error.c_str(); }
+} // namespace vptc_internal
+using vptc_internal::set_global_error;
+
+namespace {
+void* dup_aligned(const std::vector<uint8_t>& v)
+{
+    void* p = nullptr;
+    if (posix_memalign(&p, 64, v.size() ? v.size() : 64) != 0) return nullptr;
+    std::memcpy(p, v.data(), v.size());
+    return p;
+}
+} // namespace
+
+extern "C" {
+
+const char* vptc_version(void) { return "vpt-b200 0.1 (sm_100a)"; }
+
+void vptc_free(void* p) { std::free(p); }
+
+int vptc_nvdb_read_grid(const char* path, const char* grid_name, void** grid, size_t* bytes)
+{
+    if (!path || !grid_name || !grid || !bytes) { set_global_error("vptc_nvdb_read_grid: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    try {
+        const std::string err = vpt_host::read_nvdb_grid(path, grid_name, grid, bytes);
+        if (!err.empty()) {
+            set_global_error(err);
+            return err.rfind("Grid name", 0) == 0 ? VPTC_ERR_BAD_GRID : VPTC_ERR_IO;
+        }
+        if (const char* bad = vpt_host::check_grid(*grid, *bytes)) {
+            std::free(*grid); *grid = nullptr; *bytes = 0;
+            set_global_error(std::string("grid \"") + grid_name + "\": " + bad);
+            return VPTC_ERR_BAD_GRID;
+        }
+        return VPTC_OK;
+    } catch (const std::exception& e) { set_global_error(e.what()); return VPTC_ERR_IO; }
+}
+
+int vptc_nvdb_write_grids(const char* path, const void* const* grids, size_t n_grids)
+{
+    if (!path || !grids) { set_global_error("vptc_nvdb_write_grids: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    try {
+        const std::string err = vpt_host::write_nvdb_grids(path, grids, n_grids);
+        if (!err.empty()) { set_global_error(err); return VPTC_ERR_IO; }
+        return VPTC_OK;
+    } catch (const std::exception& e) { set_global_error(e.what()); return VPTC_ERR_IO; }
+}
+
+int vptc_synth_volume(const char* kind, const int32_t dims[3], double voxel_size, uint32_t seed, const double* anchor_xyz, void** density,
+                      size_t* density_bytes, void** temperature, size_t* temperature_bytes)
+{
+    if (!kind || !dims || !density || !density_bytes) { set_global_error("vptc_synth_volume: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    try {
+        vpt_host::SynthResult r = vpt_host::synth_volume(kind, dims, voxel_size, seed, anchor_xyz);
+        *density = dup_aligned(r.density); *density_bytes = r.density.size();
+        if (temperature && temperature_bytes) {
+            if (!r.temperature.empty()) { *temperature = dup_aligned(r.temperature); *temperature_bytes = r.temperature.size(); }
+            else { *temperature = nullptr; *temperature_bytes = 0; }
+        }
+        return VPTC_OK;
+    } catch (const std::exception& e) { set_global_error(e.what()); return VPTC_ERR_INVALID_ARGUMENT; }
+}
+
+int vptc_scene_from_json(const char* json_text, vptc_scene* out, char* volume_path_out, size_t volume_path_cap)
+{
+    if (!json_text || !out) { set_global_error("vptc_scene_from_json: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    std::string vol, err;
+    if (!vpt_host::parse_scene_json(json_text, *out, vol, err)) { set_global_error(err); return VPTC_ERR_CONFIG; }
+    if (volume_path_out && volume_path_cap) {
+        if (vol.size() + 1 > volume_path_cap) { set_global_error("volume_path buffer too small"); return VPTC_ERR_INVALID_ARGUMENT; }
+        std::memcpy(volume_path_out, vol.c_str(), vol.size() + 1);
+    }
+    return VPTC_OK;
+}
+
+int vptc_scene_from_json_file(const char* path, vptc_scene* out, char* volume_path_out, size_t volume_path_cap)
+{
+    if (!path || !out) { set_global_error("vptc_scene_from_json_file: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    std::string text, err;
+    if (!vpt_host::read_text_file(path, text, err)) { set_global_error(err); return VPTC_ERR_IO; }
+    const int rc = vptc_scene_from_json(text.c_str(), out, volume_path_out, volume_path_cap);
+    if (rc != VPTC_OK) set_global_error(std::string("Failed to read configuration file \"") + path + "\": " + vptc_internal::global_error());
+    return rc;
+}
+
+int vptc_write_png(const char* path, const uint8_t* rgb8, int64_t width, int64_t height)
+{
+    if (!path || !rgb8 || width <= 0 || height <= 0) { set_global_error("vptc_write_png: bad argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    std::string err;
+    if (!vpt_host::write_png_rgb8(path, rgb8, width, height, err)) { set_global_error(err); return VPTC_ERR_IO; }
+    return VPTC_OK;
+}
+
+} // extern "C"
