@@ -1,0 +1,271 @@
+"""Host-side logic and the C-ABI surface — no GPU needed.
+
+* libvptcuda.so loads and exports every symbol include/vptc.h declares; struct layouts match the header.
+* JSON scene reader = read_configuration (src/configuration.cpp:8-22): all keys mandatory; the reference's own
+  shipped scene files parse to the values volume_path_tracer_b200/scenes.py carries.
+* `.nvdb` writer/reader round trip; density required / temperature optional (src/volume_grids.cpp:36-67).
+* NanoVDB-format builder: the serialized grids are accepted by the reference's vendored NanoVDB (via oracle/_ref).
+* PNG writer (src/image_io.cpp:18-58) round trip through PIL; film_to_image oracle known answers.
+* No GPU => vptc_create fails loudly (no CPU fallback).
+"""
+import ctypes as C
+import json
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def test_abi_exports_every_declared_symbol(api):
+    header = (ROOT / "include" / "vptc.h").read_text()
+    declared = re.findall(r"VPTC_API\s+[\w\s\*]+?\b(vptc_\w+)\s*\(", header)
+    assert len(declared) >= 20 and len(set(declared)) == len(declared)
+    L = api.lib()
+    for name in declared:
+        assert hasattr(L, name), f"libvptcuda.so does not export {name}"
+    assert sorted(declared) == sorted(api.EXPORTS), "api.EXPORTS out of date with include/vptc.h"
+    assert b"sm_100a" in L.vptc_version()
+
+
+def test_abi_struct_layout(api):
+    # natural alignment of the C structs in include/vptc.h
+    assert C.sizeof(api.CameraParameters) == 44
+    assert C.sizeof(api.InfiniteLight) == 16 and C.sizeof(api.DistantLight) == 28
+    assert C.sizeof(api.VolumeParameters) == 24
+    assert C.sizeof(api.WorkerParameters) == 80
+    assert C.sizeof(api.Scene) == 200
+    assert C.sizeof(api.Counters) == 56
+
+
+def test_abi_struct_layout_matches_c_compiler(api, tmp_path):
+    """sizeof/offsetof as gcc sees include/vptc.h == the ctypes mirror."""
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "vptc.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(vptc_scene), offsetof(vptc_scene, camera_parameters), offsetof(vptc_scene, worker_parameters),'
+                   'offsetof(vptc_scene, volume_parameters), offsetof(vptc_worker_parameters, distant_light),'
+                   'offsetof(vptc_worker_parameters, max_depth), sizeof(vptc_counters));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.run(["gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    S, Wp = api.Scene, api.WorkerParameters
+    assert got == [C.sizeof(S), S.camera_parameters.offset, S.worker_parameters.offset, S.volume_parameters.offset,
+                   Wp.distant_light.offset, Wp.max_depth.offset, C.sizeof(api.Counters)]
+
+
+def test_library_has_sm100a_code_only():
+    import subprocess
+    out = subprocess.run(["/usr/local/cuda/bin/cuobjdump", "--list-elf", str(ROOT / "volume_path_tracer_b200" / "libvptcuda.so")],
+                         capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_no_gpu_fails_loudly(api):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(api.VptError) as e:
+        api.Renderer(0)
+    assert e.value.code == -3 and "no CPU fallback" in str(e.value)
+
+
+def test_null_arguments_are_errors_not_crashes(api):
+    L = api.lib()
+    assert L.vptc_set_volume(None, None, 0, None, 0) == -1
+    assert L.vptc_render(None, None, 1, 1, None) == -1
+    assert L.vptc_scene_from_json(None, None, None, 0) == -1
+    assert L.vptc_nvdb_read_grid(b"/nonexistent/file.nvdb", b"density", C.byref(C.c_void_p()), C.byref(C.c_size_t())) == -5
+    L.vptc_destroy(None)
+    L.vptc_free(None)
+
+
+# ---------------------------------------------------------------- scene JSON
+def test_scene_json_roundtrip(api, scenes):
+    s, vol = api.scene_from_json(scenes.config_json("fire"))
+    assert vol == "synthetic"
+    assert (s.seed, s.width, s.height, s.num_waves, s.num_workers) == (500, 700, 1000, 1024, 12)
+    assert tuple(s.tile_size) == (8, 8) and s.ntiles == 11000
+    assert tuple(s.camera_parameters.position) == (120.0, 30.0, 0.0) and s.camera_parameters.vfov_deg == 37.0
+    assert s.camera_parameters.imaging_ratio == np.float32(0.1)
+    wp, vp = s.worker_parameters, s.volume_parameters
+    assert wp.max_depth == 1000000 and wp.use_jitter == 1 and wp.single_pixel_enabled == 0 and tuple(wp.single_pixel_coord) == (239, 879)
+    assert tuple(wp.distant_light.inv_direction) == (0.5, 1.0, 0.0) and wp.distant_light.multiplier == 20.0
+    assert (vp.sigma_s, vp.sigma_a, vp.henyey_greenstein_g) == (np.float32(0.9), 2.0, np.float32(0.7))
+    assert vp.le_scale == np.float32(4e-8) and vp.temperature_offset == 300.0 and vp.temperature_scale == 43.0
+
+
+def _drop(d, path):
+    d = json.loads(json.dumps(d))
+    node = d
+    for k in path[:-1]:
+        node = node[k]
+    del node[path[-1]]
+    return d
+
+
+def test_scene_json_every_key_is_mandatory(api, scenes):
+    """glaze error_on_missing_keys = true (src/configuration.cpp:13-15)."""
+    base = json.loads(scenes.config_json("wdas_cloud"))
+
+    def paths(d, prefix=()):
+        for k, v in d.items():
+            yield prefix + (k,)
+            if isinstance(v, dict):
+                yield from paths(v, prefix + (k,))
+    all_paths = list(paths(base))
+    assert len(all_paths) == 32
+    for p in all_paths:
+        with pytest.raises(api.VptError) as e:
+            api.scene_from_json(json.dumps(_drop(base, p)))
+        assert e.value.code == -6 and p[-1] in str(e.value)
+
+
+def test_scene_json_rejects_bad_input(api, scenes):
+    base = json.loads(scenes.config_json("fire"))
+    for mutate in (lambda d: d.__setitem__("output_size", [700]), lambda d: d.__setitem__("seed", "x"),
+                   lambda d: d["camera_parameters"].__setitem__("up", [0, 1]), lambda d: d.__setitem__("unknown_key", 1)):
+        d = json.loads(json.dumps(base)); mutate(d)
+        with pytest.raises(api.VptError):
+            api.scene_from_json(json.dumps(d))
+    with pytest.raises(api.VptError):
+        api.scene_from_json("{ not json")
+    with pytest.raises(api.VptError):
+        api.read_configuration("/nonexistent/scene.json")
+
+
+@pytest.mark.parametrize("name", ["fire", "fire_lowscattering", "wdas_cloud"])
+def test_reference_scene_files_parse_to_our_configs(api, scenes, reference_tree, name):
+    """The reference's shipped scenes go through our reader unchanged and equal scenes.py's C1-C3 (Appendix B)."""
+    ref_scene, vol = api.read_configuration(reference_tree / "scenes" / f"{name}.json")
+    ours, _ = scenes.load_config(name)
+    assert bytes(ref_scene) == bytes(ours)
+    assert vol.startswith("../volumes/")
+
+
+# ---------------------------------------------------------------- .nvdb I/O
+def test_nvdb_roundtrip_and_grid_contract(api, tmp_path):
+    grids = api.synth_volume("fire", (40, 48, 40), 0.5, 2, None)
+    assert grids.has_temperature()
+    p = tmp_path / "fire.nvdb"
+    grids.write(p)
+    back = api.VolumeGrids.read_from_file(p)
+    assert back.has_temperature()
+    assert bytes(back.density.view()) == bytes(grids.density.view())
+    assert bytes(back.temperature.view()) == bytes(grids.temperature.view())
+    # density only: temperature optional
+    q = tmp_path / "cloud.nvdb"
+    cloud = api.synth_volume("cloud", (64, 48, 64), 1.0, 2, None)
+    assert not cloud.has_temperature()
+    cloud.write(q)
+    assert not api.VolumeGrids.read_from_file(q).has_temperature()
+    # a file without "density" is fatal (volume_grids.cpp:48-56)
+    only_t = api.VolumeGrids(grids.temperature, None)
+    r = tmp_path / "t.nvdb"
+    only_t.write(r)
+    with pytest.raises(api.VptError) as e:
+        api.VolumeGrids.read_from_file(r)
+    assert e.value.code == -2 and "density" in str(e.value)
+    grids.temperature = grids.temperature  # keep alive
+    (tmp_path / "junk.nvdb").write_bytes(b"not a nanovdb file at all" * 10)
+    with pytest.raises(api.VptError):
+        api.VolumeGrids.read_from_file(tmp_path / "junk.nvdb")
+
+
+def test_grid_header_fields(api):
+    g = api.synth_volume("dense", (32, 32, 32), 0.5, 1, (1.0, 2.0, 3.0))
+    b = g.density.view()
+    assert bytes(b[:8]) == b"NanoVDB1"
+    name = bytes(b[40:40 + 8]).split(b"\0")[0]
+    assert name == b"density"
+    vox = np.frombuffer(bytes(b[608:632]), np.float64)
+    assert np.allclose(vox, 0.5)
+    assert int(np.frombuffer(bytes(b[32:40]), np.uint64)[0]) == g.density.nbytes
+
+
+def test_synth_is_deterministic(api):
+    a = api.synth_volume("cloud", (96, 64, 96), 1.0, 5, None)
+    b = api.synth_volume("cloud", (96, 64, 96), 1.0, 5, None)
+    c = api.synth_volume("cloud", (96, 64, 96), 1.0, 6, None)
+    assert bytes(a.density.view()) == bytes(b.density.view())
+    assert bytes(a.density.view()) != bytes(c.density.view())
+    with pytest.raises(api.VptError):
+        api.synth_volume("nonsense", (8, 8, 8), 1.0, 1, None)
+
+
+def test_reference_nanovdb_accepts_our_files(api, oracle, oracle_ref, tmp_path):
+    """A grid written by our builder + .nvdb writer, read back by our reader, is walked identically by the
+    reference's vendored NanoVDB accessor (oracle/_ref) and by our own tree walker."""
+    grids = api.synth_volume("torus", (120, 60, 120), 1.0, 1, None)
+    p = tmp_path / "torus.nvdb"
+    grids.write(p)
+    back = api.VolumeGrids.read_from_file(p)
+    a, b = oracle.volume(back), oracle_ref.volume(back)
+    pts = (np.random.default_rng(0).random((30000, 3)).astype(np.float32) * 2 - 1) * np.array([120, 60, 120], np.float32)
+    va, vb = a.sample_grid(0, pts), b.sample_grid(0, pts)
+    for x, y in zip(va, vb):
+        assert np.array_equal(x, y)
+    assert (va[0] > 0).mean() > 0.01
+    assert np.array_equal(a.leaf_maxima(), b.leaf_maxima())
+
+
+# ---------------------------------------------------------------- PNG + film_to_image
+def test_png_roundtrip(api, tmp_path):
+    from PIL import Image
+    rgb = np.random.default_rng(0).integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    api.write_png(tmp_path / "a.png", rgb)
+    img = Image.open(tmp_path / "a.png")
+    assert img.mode == "RGB" and img.size == (53, 37)
+    assert np.array_equal(np.asarray(img), rgb)
+
+
+def test_film_to_image_known_answers(oracle):
+    """src/main.cpp:12-24 + include/vpt/color.hpp:8-30: XYZ/N -> linear sRGB -> OETF -> clamp -> *255 -> truncate."""
+    film = np.zeros((1, 4, 4), np.float32)
+    film[0, 0] = (0.95047 * 3, 1.0 * 3, 1.08883 * 3, 3)   # D65 white, 3 samples -> (255,255,255) up to truncation
+    film[0, 1] = (0, 0, 0, 5)                               # black
+    film[0, 2] = (0.4124 * 2, 0.2126 * 2, 0.0193 * 2, 2)    # sRGB red primary
+    film[0, 3] = (100, 100, 100, 1)                         # clamps
+    rgb = oracle.film_to_image(film)
+    assert rgb[0, 0].min() >= 254
+    assert rgb[0, 1].tolist() == [0, 0, 0]
+    assert rgb[0, 2, 0] >= 254 and rgb[0, 2, 1] <= 2 and rgb[0, 2, 2] <= 2
+    assert rgb[0, 3].tolist() == [255, 255, 255]
+
+
+# ---------------------------------------------------------------- camera (src/camera.cpp:5-57)
+def test_camera_rays(oracle, scenes):
+    s, _ = scenes.load_config("fire")
+    W, H = s.width, s.height
+    px = np.array([0, W - 1, 0, W - 1, W // 2]); py = np.array([0, 0, H - 1, H - 1, H // 2])
+    o, d = oracle.camera_rays(s, px, py, np.zeros(5, np.float32), np.zeros(5, np.float32))
+    assert np.array_equal(o, np.tile(np.array([[120, 30, 0]], np.float32), (5, 1)))
+    assert np.allclose(np.linalg.norm(d, axis=1), 1, atol=1e-6)
+    # centre pixel looks (almost) along look - position = -x
+    assert d[4, 0] < -0.9999
+    # raster (0,0) maps toward +left and +new_up (camera.cpp:21-31): up = +y; left = up x dir = (0,1,0)x(-1,0,0) = (0,0,1)
+    assert d[0, 1] > 0 and d[0, 2] > 0 and d[3, 1] < 0 and d[3, 2] < 0
+    # vertical half-angle = vfov/2 at the top edge (pixel centre offset 0.5)
+    o2, d2 = oracle.camera_rays(s, np.array([W // 2]), np.array([0]), np.array([-0.5], np.float32), np.array([-0.5], np.float32))
+    ang = np.degrees(np.arctan2(d2[0, 1], -d2[0, 0]))
+    assert abs(ang - 18.5) < 0.05
+
+
+# ---------------------------------------------------------------- tile/wave job space (src/tile_provider.cpp:14-105)
+def test_ragged_tiles_cover_image_once(oracle, api, scenes):
+    scene, spec = scenes.small_variant("fire", (37, 29), 3, 0.2)
+    scene.tile_size[0], scene.tile_size[1] = 8, 5
+    assert scene.ntiles == 5 * 6
+    grids = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
+    vol = oracle.volume(grids)
+    film = np.zeros((29, 37, 4), np.float32)
+    vol.render(scene, film, threads=4)
+    assert (film[..., 3] == 3).all()
+    # waves are additive: [1..3] == [1..2] + [3]
+    a = np.zeros_like(film); vol.render(scene, a, first_wave=1, n_waves=2); vol.render(scene, a, first_wave=3, n_waves=1)
+    assert np.array_equal(a, film)
