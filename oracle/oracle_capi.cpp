@@ -96,6 +96,22 @@ int vpto_render(void* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_
     return 0;
 }
 
+// Bounded sample for the timed CPU baseline: every job_stride-th job of the wave range (see render()).
+// With job_stride > 1 two threads may hit the same tile in different waves; the film is then only a timing
+// by-product (callers pass a scratch film), the counters stay exact.
+int vpto_render_sample(void* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, uint64_t job_stride, uint32_t num_threads,
+                       float* film, vptc_counters* counters, double* seconds)
+{
+    auto* c = static_cast<Ctx*>(ctx);
+    if (!c || !scene || !film || first_wave < 1 || num_threads < 1 || job_stride < 1) return -1;
+    Volume<S> vol = make_volume(c, scene->volume_parameters);
+    Counters cnt;
+    const double s = render<S>(*scene, vol, first_wave, n_waves, num_threads, film, &cnt, job_stride);
+    copy_counters(cnt, counters);
+    if (seconds) *seconds = s;
+    return 0;
+}
+
 int vpto_trace_jobs(void* ctx, const vptc_scene* scene, const uint64_t* jids, size_t n_jobs, float* per_pixel_xyz, uint32_t* per_pixel_ndraws,
                     vptc_counters* counters)
 {

@@ -23,9 +23,21 @@ REFERENCE_ROOT = Path(os.environ.get("VPT_REFERENCE_DIR", "/root/reference"))
 
 def build(ref: bool = True) -> None:
     """make the oracle libraries (the checker). `ref` is skipped when the reference tree is absent."""
-    subprocess.run(["make", "-C", str(_DIR), "-s", "libvpt_oracle.so"], check=True)
+    subprocess.run(["make", "-C", str(_DIR), "-s", "libvpt_oracle.so", "libvpt_libm_check.so"], check=True)
     if ref and (REFERENCE_ROOT / "external" / "openvdb" / "nanovdb").is_dir():
         subprocess.run(["make", "-C", str(_DIR), "-s", "ref", f"REF={REFERENCE_ROOT}"], check=True)
+
+
+def libm_check(stride: int = 1):
+    """Sweep the device's glibc-exact logf/sinf/cosf restatement (compiled for the host) against this machine's
+    libm. -> (n_logf, mismatches_logf, n_sincos, mismatches_sincos); stride 1 is exhaustive (~20-40 s)."""
+    path = _DIR / "libvpt_libm_check.so"
+    if not path.exists():
+        build(ref=False)
+    L = C.CDLL(str(path))
+    out = (C.c_uint64 * 4)()
+    L.vptm_check(C.c_uint32(stride), out)
+    return tuple(int(x) for x in out)
 
 
 def _ptr(a):
@@ -50,6 +62,7 @@ class Oracle:
         L.vpto_destroy.restype = None
         L.vpto_leaf_maxima.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
         L.vpto_render.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, C.POINTER(C.c_double)]
+        L.vpto_render_sample.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, vp, vp, C.POINTER(C.c_double)]
         L.vpto_trace_jobs.argtypes = [vp, vp, vp, sz, vp, vp, vp]
         L.vpto_trace_segments.argtypes = [vp, vp, vp, sz, C.c_uint32, vp, vp]
         L.vpto_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
@@ -150,6 +163,16 @@ class OracleVolume:
                                 C.addressof(c), C.byref(secs))
         if rc != 0:
             raise RuntimeError(f"vpto_render failed ({rc})")
+        return secs.value, c
+
+    def render_sample(self, scene, film: np.ndarray, first_wave: int, n_waves: int, job_stride: int, threads: int | None = None):
+        """Timed CPU-baseline leg: every job_stride-th (tile, wave) job of the range. -> (seconds, counters)."""
+        from volume_path_tracer_b200.api import Counters
+        c, secs = Counters(), C.c_double()
+        threads = threads or os.cpu_count() or 1
+        rc = self.L.vpto_render_sample(self.ctx, C.addressof(scene), first_wave, n_waves, job_stride, threads, _ptr(film), C.addressof(c), C.byref(secs))
+        if rc != 0:
+            raise RuntimeError(f"vpto_render_sample failed ({rc})")
         return secs.value, c
 
     def trace_jobs(self, scene, jids):

@@ -255,13 +255,16 @@ void run_job(const vptc_scene& scene, const Volume<S>& vol, const Camera& camera
 // Multi-threaded render of waves [first_wave, first_wave+n_waves): the reference's worker loop
 // (main.cpp:63-87) with TileProvider's ordering guarantee — a tile's waves are processed in order and
 // never concurrently (tile_provider.cpp:40-60) — so the film is bit-deterministic.
+// `job_stride` > 1 renders only every job_stride-th job of the range (a bounded, frame-covering SAMPLE of the
+// workload for the timed CPU baseline); pick it coprime to ntiles so successive waves visit different tiles.
 template <class S>
 double render(const vptc_scene& scene, const Volume<S>& vol, uint32_t first_wave, uint32_t n_waves, unsigned num_threads, float* film,
-              Counters* total)
+              Counters* total, uint64_t job_stride = 1)
 {
     const TileGrid tg(scene);
     const Camera camera(scene.camera_parameters, tg.W, tg.H);
-    const uint64_t ntiles = tg.ntiles(), njobs = ntiles * n_waves, job0 = uint64_t(first_wave - 1) * ntiles;
+    const uint64_t ntiles = tg.ntiles(), njobs_all = ntiles * n_waves, job0 = uint64_t(first_wave - 1) * ntiles;
+    const uint64_t njobs = (njobs_all + job_stride - 1) / job_stride;
     std::atomic<uint64_t> job_idx{0};
     std::vector<std::atomic<uint32_t>> tile_wave(ntiles);
     for (auto& t : tile_wave) t.store(first_wave - 1);
@@ -275,9 +278,11 @@ double render(const vptc_scene& scene, const Volume<S>& vol, uint32_t first_wave
         for (;;) {
             const uint64_t j = job_idx.fetch_add(1, std::memory_order_relaxed);
             if (j >= njobs) break;
-            const uint64_t jid = job0 + j, tile = jid % ntiles;
+            const uint64_t jid = job0 + j * job_stride, tile = jid % ntiles;
             const uint32_t wave = uint32_t(1 + jid / ntiles);
-            while (tile_wave[tile].load(std::memory_order_acquire) != wave - 1) std::this_thread::yield();
+            // per-tile wave ordering (tile_provider.cpp:40-60); with a job stride a tile may skip waves, so wait
+            // only until no EARLIER wave of this tile is still in flight (the counter holds the last finished one)
+            if (job_stride == 1) while (tile_wave[tile].load(std::memory_order_acquire) != wave - 1) std::this_thread::yield();
             run_job<S>(scene, vol, camera, tg, jid, rng, density_acc, vol.m_has_temp ? &temp_sampler : nullptr, film, nullptr, nullptr, &cnts[tid]);
             tile_wave[tile].store(wave, std::memory_order_release);
         }

@@ -4,13 +4,15 @@
 // square root (nvcc defaults -prec-div=true -prec-sqrt=true, no -use_fast_math, denormals kept), so every
 // + - * / sqrt floor rounds exactly as the reference's baseline-x86-64 Release build does; the only fused
 // operations are the explicit fmaf calls NanoVDB itself makes (NV/math/Ray.h:154-159, Math.h:905-939).
-// logf / sinf / cosf are CUDA's (<= 1-2 ulp from glibc's): the one source of rare branch flips.
+// logf / sinf / cosf are NOT CUDA's: libm_exact.cuh restates glibc's double-precision table+polynomial schemes,
+// verified exhaustively on the argument domains used here, so branch decisions match the CPU reference.
 #pragma once
 #include <cfloat>
 #include <cstdint>
 #include <cuda_runtime.h>
 
 #include "layout.hpp"
+#include "libm_exact.cuh"
 
 namespace vptd {
 
@@ -263,7 +265,7 @@ struct Collision { V3 point; float sigma_maj, density; };
 
 // MajorantTransmittanceSampler::next   src/majorant_transmittance_sampler.cpp:21-81
 template <bool COUNT>
-__device__ __forceinline__ bool sampler_next(March& m, const GridDev& G, Rng& rng, float sigma_t, Collision& out, Stats& st)
+__device__ __forceinline__ bool sampler_next(March& m, const GridDev& G, Rng& rng, float sigma_t, const double* logtab, Collision& out, Stats& st)
 {
     for (;;) {
         if (!m.has_seg) {
@@ -272,7 +274,7 @@ __device__ __forceinline__ bool sampler_next(March& m, const GridDev& G, Rng& rn
             m.has_seg = true;
         }
         const float sigma_maj = m.seg_dmaj * sigma_t;
-        const float dt_m = -logf(1.0f - rng.uniform()) / sigma_maj; // sample_exponential  random.hpp:19-22
+        const float dt_m = -vptm::logf_exact(1.0f - rng.uniform(), logtab) / sigma_maj; // sample_exponential  random.hpp:19-22
         const float t = m.seg_t0 + dt_m / m.scale;
         if (t < m.seg_t1) {
             m.seg_t0 = t;
@@ -308,7 +310,9 @@ __device__ __forceinline__ V3 sample_henyey_greenstein(V3 w, float ux, float uy,
     const float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
     const float phi = 6.2831854820251465f * uy; // 2.0f * float(pi) * u.y
     const float st = fminf(fmaxf(sin_theta, -1.0f), 1.0f), ct = fminf(fmaxf(cos_theta, -1.0f), 1.0f);
-    V3 local = normalized(mk(st * cosf(phi), st * sinf(phi), ct));
+    float sphi, cphi;
+    vptm::sincosf_exact(phi, sphi, cphi);
+    V3 local = normalized(mk(st * cphi, st * sphi, ct));
     // coordinate_system(z = w, x, y)
     const float sign = copysignf(1.0f, w.z);
     const float a = -1.0f / (sign + w.z);

@@ -14,6 +14,7 @@
 namespace vptd {
 
 __constant__ float c_cie[471 * 3];
+__constant__ double c_logf_table[32] = VPT_LOGF_TABLE_INIT;
 
 // ---------------------------------------------------------------- blackbody  src/precompute_blackbody.cpp:24-52
 __device__ __noinline__ V3 spectrum_to_xyz_direct(float T) // T >= 49900 K: direct 471-term integration (spectral.hpp:62-75)
@@ -52,7 +53,7 @@ __device__ __forceinline__ V3 blackbody_xyz(const float* __restrict__ bb, float 
 
 // ---------------------------------------------------------------- sample_Ld  src/worker.cpp:52-90
 template <bool COUNT>
-__device__ __forceinline__ V3 sample_Ld(const RenderArgs& A, Rng& rng, V3 pos, V3 w, Stats& st)
+__device__ __forceinline__ V3 sample_Ld(const RenderArgs& A, const double* logtab, Rng& rng, V3 pos, V3 w, Stats& st)
 {
     const SceneDev& S = A.scene;
     if (!S.dist_light_on) return mk(0.0f, 0.0f, 0.0f);
@@ -62,7 +63,7 @@ __device__ __forceinline__ V3 sample_Ld(const RenderArgs& A, Rng& rng, V3 pos, V
     March m;
     if (march_begin(m, A.density, pos, wi)) {
         Collision c;
-        while (sampler_next<COUNT>(m, A.density, rng, S.sigma_t, c, st)) {
+        while (sampler_next<COUNT>(m, A.density, rng, S.sigma_t, logtab, c, st)) {
             const float sigma_n = fmaxf(0.0f, c.sigma_maj - S.sigma_t * c.density);
             T_ray *= sigma_n / c.sigma_maj;
             if (T_ray <= 0.05f) {
@@ -79,7 +80,7 @@ __device__ __forceinline__ V3 sample_Ld(const RenderArgs& A, Rng& rng, V3 pos, V
 
 // ---------------------------------------------------------------- one camera path  src/worker.cpp:121-200
 template <bool COUNT>
-__device__ __forceinline__ V3 trace_pixel(const RenderArgs& A, const float* __restrict__ bb, Rng& rng, int64_t px, int64_t py, Stats& st)
+__device__ __forceinline__ V3 trace_pixel(const RenderArgs& A, const float* __restrict__ bb, const double* logtab, Rng& rng, int64_t px, int64_t py, Stats& st)
 {
     const SceneDev& S = A.scene;
     const float j0 = rng.uniform(), j1 = rng.uniform();
@@ -98,7 +99,7 @@ __device__ __forceinline__ V3 trace_pixel(const RenderArgs& A, const float* __re
         March m;
         if (!march_begin(m, A.density, ro, rd)) break;
         Collision c;
-        while (sampler_next<COUNT>(m, A.density, rng, S.sigma_t, c, st)) {
+        while (sampler_next<COUNT>(m, A.density, rng, S.sigma_t, logtab, c, st)) {
             const float p_a = (S.sigma_a * c.density) / c.sigma_maj;
             const float p_s = (S.sigma_s * c.density) / c.sigma_maj;
             const float p_n = fmaxf(1.0f - p_a - p_s, 0.0f);
@@ -121,7 +122,7 @@ __device__ __forceinline__ V3 trace_pixel(const RenderArgs& A, const float* __re
             if (event == 2) {
                 if (depth++ >= S.max_depth) { terminated = true; break; }
                 if (COUNT) ++st.scatter_events;
-                const V3 ld = sample_Ld<COUNT>(A, rng, c.point, rd, st);
+                const V3 ld = sample_Ld<COUNT>(A, logtab, rng, c.point, rd, st);
                 L.x += ld.x; L.y += ld.y; L.z += ld.z;
                 const float u0 = rng.uniform(), u1 = rng.uniform();
                 rd = sample_henyey_greenstein(rd, u0, u1, S.g);
@@ -150,7 +151,9 @@ template <bool TRACE, bool COUNT>
 __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_kernel(const RenderArgs A)
 {
     __shared__ float bb[1504]; // precompute_blackbody table: 500 x XYZ (+1 padding entry, see oracle note)
+    __shared__ double logtab[32]; // glibc logf's {1/c, log c} table (libm_exact.cuh)
     for (int i = threadIdx.x; i < 1504; i += blockDim.x) bb[i] = i < 1500 ? A.bb_table[i] : 0.0f;
+    if (threadIdx.x < 32) logtab[threadIdx.x] = c_logf_table[threadIdx.x];
     __syncthreads();
 
     const SceneDev& S = A.scene;
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_kernel(const Ren
             for (int x = 0; x < sx; ++x) {
                 const int64_t px = x0 + x, py = y0 + y;
                 if (S.single_pixel_enabled && (px != S.single_pixel_x || py != S.single_pixel_y)) continue;
-                const V3 L = trace_pixel<COUNT>(A, bb, rng, px, py, st);
+                const V3 L = trace_pixel<COUNT>(A, bb, logtab, rng, px, py, st);
                 if (TRACE) {
                     const size_t slot = size_t(j) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
                     A.trace_xyz[slot * 3 + 0] = L.x; A.trace_xyz[slot * 3 + 1] = L.y; A.trace_xyz[slot * 3 + 2] = L.z;
