@@ -122,6 +122,11 @@ VPTC_API int   vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out);
 /* Counting costs atomics; off by default. */
 VPTC_API int   vptc_enable_counters(vptc_ctx* ctx, int enabled);
 
+/* Which render kernel runs: 1 (default) = flat state-machine megakernel, 0 = the first nested megakernel
+ * (kept so the design choice stays measurable: profiles/). Both produce the same film bit for bit per sample.
+ * The environment variable VPT_KERNEL_VARIANT sets the default at vptc_create. */
+VPTC_API int   vptc_set_kernel_variant(vptc_ctx* ctx, int variant);
+
 /* Parity hook = the reference's single_pixel / Logger<true> debugging aids (worker.cpp:15-49,113-119):
  * runs the given jobs and returns, per job and per pixel of its tile (row-major inside the tile,
  * tile_w*tile_h slots per job, unused slots of clipped tiles zero), the un-scaled radiance L (XYZ)

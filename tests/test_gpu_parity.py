@@ -94,7 +94,8 @@ def test_tiles_volume_bit_exact(renderer, oracle, api):
 
 
 # minimum fraction of JOBS (64 pixels sharing one RNG stream) whose draw counts all agree with the oracle
-MIN_AGREE = {"fire": 0.97, "fire_lowscattering": 0.97, "wdas_cloud": 0.9, "dense512": 0.3}
+# (the device's logf/sinf/cosf are glibc-exact — csrc/device/libm_exact.cuh — so every job agrees in practice)
+MIN_AGREE = {"fire": 0.999, "fire_lowscattering": 0.999, "wdas_cloud": 0.999, "dense512": 0.999}
 
 
 @pytest.mark.parametrize("name", list(SMALL))
@@ -125,7 +126,7 @@ def test_per_job_radiance_parity(renderer, oracle, loaded, gold, name):
 
 @pytest.mark.parametrize("name", list(SMALL))
 def test_film_and_counters(renderer, oracle, loaded, gold, name):
-    """vptc_render adds (imaging_ratio*L, 1) per sample: counts exact, sums close, work counters within 2 %."""
+    """vptc_render adds (imaging_ratio*L, 1) per sample: counts exact, sums close, work counters equal the oracle's."""
     scene, spec, grids = loaded(name)
     renderer.enable_counters(True)
     film = renderer.run(scene, renderer.new_film(scene))
@@ -137,7 +138,7 @@ def test_film_and_counters(renderer, oracle, loaded, gold, name):
     wc = dict(zip(c.keys(), gold[f"{name}_film_counters"].tolist()))
     assert c["pixel_samples"] == wc["pixel_samples"]
     for k in ("density_evals", "majorant_fetches", "rng_draws", "temperature_evals"):
-        assert abs(c[k] - wc[k]) <= 0.02 * max(wc[k], 1), (k, c[k], wc[k])
+        assert c[k] == wc[k], (k, c[k], wc[k])  # same branch decisions => same work, exactly
     # most pixels are bit-close; the rest differ by whole paths where a branch flipped
     close = np.isclose(film[..., :3], want[..., :3], rtol=1e-4, atol=1e-7).all(axis=-1)
     assert close.mean() >= MIN_AGREE[name] * 0.9
@@ -254,36 +255,61 @@ def test_errors(renderer, api, scenes):
     r2.close()
 
 
-@pytest.mark.parametrize("name,waves_cpu,waves_gpu", [("fire", 48, 48), ("wdas_cloud", 48, 48)])
-def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves_cpu, waves_gpu):
-    """Converged-image criterion at test size: GPU film vs the CPU oracle film rendered with DIFFERENT waves
-    (independent samples), per-pixel difference inside 3 sigma, relMSE stated. sigma is estimated per pixel from
-    per-wave luminance films of the oracle."""
+@pytest.mark.parametrize("name,waves", [("fire", 48), ("wdas_cloud", 48)])
+def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
+    """Converged-image criterion at test size: the GPU film of waves 1000.. against the CPU oracle film of waves
+    1.. (INDEPENDENT samples): per-pixel difference inside 3 sigma, relMSE stated. sigma is estimated per pixel from
+    the per-wave luminance of both sets. Path radiance is heavy-tailed (rare bright emission / sun hits), so the
+    fraction inside 3 estimated sigma sits below the Gaussian 0.9973; the CONTROL is the CPU oracle rendering waves
+    1000.. itself: the GPU must score like the control (it is the same estimator), and both above 0.95."""
     scene, spec, grids = loaded(name)
     vol = oracle.volume(grids)
     s = scene.copy()
     H, W = s.height, s.width
-    per_wave = np.zeros((waves_cpu, H, W), np.float64)
-    cpu = np.zeros((H, W, 4), np.float32)
-    for k in range(waves_cpu):
-        f = np.zeros((H, W, 4), np.float32)
-        vol.render(s, f, first_wave=1 + k, n_waves=1)
-        per_wave[k] = f[..., 1]
-        cpu += f
-    gpu = renderer.run(s, renderer.new_film(s), first_wave=1000, n_waves=waves_gpu)
-    mc, mg = cpu[..., 1] / cpu[..., 3], gpu[..., 1] / gpu[..., 3]
-    var = per_wave.var(axis=0, ddof=1)
-    sigma = np.sqrt(var / waves_cpu + var / waves_gpu)
-    floor = 1e-3 * max(mc.mean(), 1e-12)  # pixels with ~zero sample variance (all paths identical)
-    z = np.abs(mc - mg) / np.maximum(sigma, floor)
-    frac3 = (z <= 3).mean()
-    relmse = np.mean((mg - mc) ** 2 / (mc ** 2 + 1e-4 * mc.mean() ** 2))
-    print(f"\n[{name}] {W}x{H}, {waves_cpu} cpu waves vs {waves_gpu} gpu waves: within 3 sigma {frac3:.4f}, max z {z.max():.2f}, relMSE {relmse:.4g}, "
-          f"mean cpu {mc.mean():.5f} gpu {mg.mean():.5f}")
-    assert frac3 >= 0.985   # Gaussian expectation 0.9973; heavy-tailed path radiance + estimated sigma
-    assert abs(mg.mean() - mc.mean()) <= 4 * np.sqrt((sigma ** 2).sum()) / sigma.size + 1e-3 * mc.mean()
-    # same waves on both sides: the images coincide except where a branch flipped
-    same = renderer.run(s, renderer.new_film(s), first_wave=1, n_waves=waves_cpu)
-    rel = np.mean((same[..., 1] - cpu[..., 1]) ** 2) / np.mean(cpu[..., 1] ** 2)
-    print(f"[{name}] same-wave relMSE {rel:.3g}")
-    assert rel < 1e-2
+
+    def per_wave_cpu(first):
+        pw = np.zeros((waves, H, W), np.float64)
+        for k in range(waves):
+            f = np.zeros((H, W, 4), np.float32)
+            vol.render(s, f, first_wave=first + k, n_waves=1)
+            pw[k] = f[..., 1]
+        return pw
+    a, c = per_wave_cpu(1), per_wave_cpu(1000)
+    gpu = renderer.run(s, renderer.new_film(s), first_wave=1000, n_waves=waves)
+    assert (gpu[..., 3] == waves).all()
+    ma, mc, mg = a.mean(axis=0), c.mean(axis=0), gpu[..., 1].astype(np.float64) / waves
+    var = np.concatenate([a, c]).var(axis=0, ddof=1)
+    sigma = np.sqrt(2 * var / waves)
+    floor = 1e-3 * max(ma.mean(), 1e-12)  # pixels with ~zero sample variance (all paths identical)
+
+    def score(m):
+        z = np.abs(m - ma) / np.maximum(sigma, floor)
+        return (z <= 3).mean(), np.mean((m - ma) ** 2 / (ma ** 2 + 1e-4 * ma.mean() ** 2))
+    (f_gpu, r_gpu), (f_cpu, r_cpu) = score(mg), score(mc)
+    print(f"\n[{name}] {W}x{H}, {waves} vs {waves} independent waves: GPU within 3 sigma {f_gpu:.4f} (CPU control {f_cpu:.4f}), "
+          f"relMSE GPU {r_gpu:.4g} (control {r_cpu:.4g}), mean cpu {ma.mean():.5f} gpu {mg.mean():.5f}")
+    assert f_gpu >= 0.95 and abs(f_gpu - f_cpu) <= 0.003
+    assert abs(r_gpu - r_cpu) <= 0.02 * max(r_cpu, 1e-6)
+    # same waves on both sides: the GPU film IS the CPU film up to fp32 add order
+    assert np.allclose(mg, mc, rtol=1e-5, atol=1e-9)
+
+
+@pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
+def test_kernel_variants_agree(renderer, loaded, name):
+    """The nested (0) and the flat state-machine (1) megakernels are two schedules of the same arithmetic:
+    per-job radiance and RNG draw counts must be bit-identical."""
+    scene, spec, grids = loaded(name)
+    jids = np.arange(scene.ntiles * scene.num_waves, dtype=np.uint64)
+    try:
+        renderer.set_kernel_variant(0)
+        x0, n0 = renderer.trace_jobs(scene, jids)
+        renderer.enable_counters(True); f0 = renderer.run(scene, renderer.new_film(scene)); c0 = renderer.counters().as_dict()
+        renderer.set_kernel_variant(1)
+        x1, n1 = renderer.trace_jobs(scene, jids)
+        f1 = renderer.run(scene, renderer.new_film(scene)); c1 = renderer.counters().as_dict()
+    finally:
+        renderer.enable_counters(False)
+        renderer.set_kernel_variant(1)
+    assert np.array_equal(n0, n1) and np.array_equal(x0, x1)
+    assert c0 == c1
+    assert np.array_equal(f0[..., 3], f1[..., 3]) and np.allclose(f0, f1, rtol=1e-5, atol=1e-7)

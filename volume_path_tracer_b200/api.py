@@ -89,7 +89,7 @@ class VptError(RuntimeError):
 
 EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms",
-    "vptc_get_counters", "vptc_enable_counters", "vptc_trace_jobs", "vptc_trace_segments", "vptc_sample_grid", "vptc_film_to_image",
+    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_sample_grid", "vptc_film_to_image",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_version",
 ]
@@ -120,6 +120,7 @@ def lib() -> C.CDLL:
     L.vptc_last_render_ms.restype = C.c_float
     L.vptc_get_counters.argtypes = [vp, C.POINTER(Counters)]
     L.vptc_enable_counters.argtypes = [vp, C.c_int]
+    L.vptc_set_kernel_variant.argtypes = [vp, C.c_int]
     L.vptc_trace_jobs.argtypes = [vp, C.POINTER(Scene), vp, sz, vp, vp]
     L.vptc_trace_segments.argtypes = [vp, vp, vp, sz, u32, vp, vp]
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
@@ -153,9 +154,12 @@ class GridBuffer:
         self.ptr, self.nbytes = ptr, nbytes
 
     def __del__(self):
-        if getattr(self, "ptr", None):
-            lib().vptc_free(self.ptr)
-            self.ptr = None
+        try:
+            if getattr(self, "ptr", None):
+                lib().vptc_free(self.ptr)
+                self.ptr = None
+        except Exception:  # interpreter shutdown
+            pass
 
     def view(self) -> np.ndarray:
         return np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr))
@@ -243,6 +247,10 @@ class Renderer:
 
     def enable_counters(self, on: bool = True):
         _check(lib().vptc_enable_counters(self._ctx, int(on)), self._ctx)
+
+    def set_kernel_variant(self, variant: int):
+        """1 = flat state-machine megakernel (default), 0 = first nested megakernel."""
+        _check(lib().vptc_set_kernel_variant(self._ctx, int(variant)), self._ctx)
 
     def counters(self) -> Counters:
         c = Counters()

@@ -146,7 +146,11 @@ __device__ __forceinline__ void film_add(float* film, float x, float y, float z)
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(film), "f"(x), "f"(y), "f"(z), "f"(1.0f) : "memory");
 }
 
-// ---------------------------------------------------------------- the megakernel
+} // namespace vptd
+#include "vpt_render_flat.cuh" // variant 1 (default): the flat state-machine megakernel
+namespace vptd {
+
+// ---------------------------------------------------------------- variant 0: the first, nested megakernel (kept for the ncu comparison)
 template <bool TRACE, bool COUNT>
 __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_kernel(const RenderArgs A)
 {
@@ -250,26 +254,30 @@ __global__ void vpt_resolve_kernel(const float4* film, size_t n, uint8_t* rgb)
 // ---------------------------------------------------------------- launchers
 cudaError_t upload_cie_table(const float* cie471x3) { return cudaMemcpyToSymbol(c_cie, cie471x3, sizeof(float) * 471 * 3); }
 
-cudaError_t launch_render(const RenderArgs& args, bool trace, bool count, int grid_blocks, cudaStream_t stream)
+template <bool TRACE, bool COUNT>
+static void launch_variant(const RenderArgs& args, int variant, int grid_blocks, cudaStream_t stream)
 {
-    if (trace) {
-        if (count) vpt_render_kernel<true, true><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-        else vpt_render_kernel<true, false><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-    } else {
-        if (count) vpt_render_kernel<false, true><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-        else vpt_render_kernel<false, false><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-    }
+    if (variant == 0) vpt_render_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else vpt_render_flat_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+}
+cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream)
+{
+    if (trace) { if (count) launch_variant<true, true>(args, variant, grid_blocks, stream); else launch_variant<true, false>(args, variant, grid_blocks, stream); }
+    else { if (count) launch_variant<false, true>(args, variant, grid_blocks, stream); else launch_variant<false, false>(args, variant, grid_blocks, stream); }
     return cudaGetLastError();
 }
-int render_blocks_per_sm(bool trace, bool count)
+template <bool TRACE, bool COUNT>
+static int occupancy_variant(int variant)
 {
     int n = 0;
-    cudaError_t e;
-    if (trace) e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<true, true>, VPT_BLOCK_THREADS, 0)
-                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<true, false>, VPT_BLOCK_THREADS, 0);
-    else e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<false, true>, VPT_BLOCK_THREADS, 0)
-                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<false, false>, VPT_BLOCK_THREADS, 0);
+    const cudaError_t e = variant == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
+                                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_flat_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0);
     return e == cudaSuccess ? n : 0;
+}
+int render_blocks_per_sm(int variant, bool trace, bool count)
+{
+    if (trace) return count ? occupancy_variant<true, true>(variant) : occupancy_variant<true, false>(variant);
+    return count ? occupancy_variant<false, true>(variant) : occupancy_variant<false, false>(variant);
 }
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s)
 {

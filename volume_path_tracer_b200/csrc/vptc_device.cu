@@ -1,6 +1,7 @@
 // vptc_device.cu — the device-facing entry points of include/vptc.h: context, volume staging, render,
 // parity hooks. Plain CUDA runtime; no torch types cross this boundary.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <memory>
@@ -39,6 +40,7 @@ struct vptc_ctx {
     unsigned long long* queue = nullptr;
     CountersDev* counters = nullptr;
     bool count = false;
+    int variant = 1; // render kernel variant (vptc_set_kernel_variant)
     float last_ms = 0.0f;
     vptc_counters last_counters{};
     int num_sms = 0;
@@ -105,13 +107,13 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     A.counters = ctx->counters;
     CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
-    const int per_sm = render_blocks_per_sm(trace, ctx->count);
+    const int per_sm = render_blocks_per_sm(ctx->variant, trace, ctx->count);
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
     // persistent grid: every SM filled to its occupancy limit, never more blocks than jobs need
     unsigned long long want = (A.n_jobs + VPT_BLOCK_THREADS - 1) / VPT_BLOCK_THREADS;
     int blocks = int(std::min<unsigned long long>(want ? want : 1ULL, (unsigned long long)(ctx->num_sms) * per_sm));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_render(A, trace, ctx->count, blocks, ctx->stream));
+    CU(launch_render(A, ctx->variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     CU(cudaEventSynchronize(ctx->ev1));
     CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
@@ -156,6 +158,7 @@ int vptc_create(vptc_ctx** out, int device)
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
     CU(upload_cie_table(vpt_host::cie_table()));
+    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::atoi(v) == 0 ? 0 : 1;
     *out = c.release();
     return VPTC_OK;
 }
@@ -251,6 +254,13 @@ int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_enable_counters: ctx is null");
     ctx->count = enabled != 0;
+    return VPTC_OK;
+}
+int vptc_set_kernel_variant(vptc_ctx* ctx, int variant)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: ctx is null");
+    if (variant != 0 && variant != 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested megakernel) or 1 (flat megakernel)");
+    ctx->variant = variant;
     return VPTC_OK;
 }
 int vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out)
