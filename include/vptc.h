@@ -122,8 +122,9 @@ VPTC_API int   vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out);
 /* Counting costs atomics; off by default. */
 VPTC_API int   vptc_enable_counters(vptc_ctx* ctx, int enabled);
 
-/* Which render kernel runs: 1 (default) = flat state-machine megakernel, 0 = the first nested megakernel
- * (kept so the design choice stays measurable: profiles/). Both produce the same film bit for bit per sample.
+/* Which render kernel runs: 2 (default) = flat state machine with warp-level stage scheduling, 1 = flat state
+ * machine, 0 = the first nested megakernel (kept so the design choice stays measurable: profiles/). All produce
+ * the same film bit for bit per sample.
  * The environment variable VPT_KERNEL_VARIANT sets the default at vptc_create. */
 VPTC_API int   vptc_set_kernel_variant(vptc_ctx* ctx, int variant);
 

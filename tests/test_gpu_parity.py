@@ -296,20 +296,22 @@ def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
 
 @pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
 def test_kernel_variants_agree(renderer, loaded, name):
-    """The nested (0) and the flat state-machine (1) megakernels are two schedules of the same arithmetic:
-    per-job radiance and RNG draw counts must be bit-identical."""
+    """The nested (0), flat (1) and stage-scheduled (2) megakernels are three schedules of the same arithmetic:
+    per-job radiance, RNG draw counts and work counters must be bit-identical."""
     scene, spec, grids = loaded(name)
     jids = np.arange(scene.ntiles * scene.num_waves, dtype=np.uint64)
+    res = []
     try:
-        renderer.set_kernel_variant(0)
-        x0, n0 = renderer.trace_jobs(scene, jids)
-        renderer.enable_counters(True); f0 = renderer.run(scene, renderer.new_film(scene)); c0 = renderer.counters().as_dict()
-        renderer.set_kernel_variant(1)
-        x1, n1 = renderer.trace_jobs(scene, jids)
-        f1 = renderer.run(scene, renderer.new_film(scene)); c1 = renderer.counters().as_dict()
+        renderer.enable_counters(True)
+        for v in (0, 1, 2):
+            renderer.set_kernel_variant(v)
+            x, n = renderer.trace_jobs(scene, jids)
+            f = renderer.run(scene, renderer.new_film(scene))
+            res.append((x, n, f, renderer.counters().as_dict()))
     finally:
         renderer.enable_counters(False)
-        renderer.set_kernel_variant(1)
-    assert np.array_equal(n0, n1) and np.array_equal(x0, x1)
-    assert c0 == c1
-    assert np.array_equal(f0[..., 3], f1[..., 3]) and np.allclose(f0, f1, rtol=1e-5, atol=1e-7)
+        renderer.set_kernel_variant(2)
+    for x, n, f, c in res[1:]:
+        assert np.array_equal(n, res[0][1]) and np.array_equal(x, res[0][0])
+        assert c == res[0][3]
+        assert np.array_equal(f[..., 3], res[0][2][..., 3]) and np.allclose(f, res[0][2], rtol=1e-5, atol=1e-7)

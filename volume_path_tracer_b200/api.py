@@ -249,7 +249,7 @@ class Renderer:
         _check(lib().vptc_enable_counters(self._ctx, int(on)), self._ctx)
 
     def set_kernel_variant(self, variant: int):
-        """1 = flat state-machine megakernel (default), 0 = first nested megakernel."""
+        """2 = flat + warp-level stage scheduling (default), 1 = flat state machine, 0 = first nested megakernel."""
         _check(lib().vptc_set_kernel_variant(self._ctx, int(variant)), self._ctx)
 
     def counters(self) -> Counters:

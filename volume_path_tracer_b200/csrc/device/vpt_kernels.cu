@@ -147,7 +147,8 @@ __device__ __forceinline__ void film_add(float* film, float x, float y, float z)
 }
 
 } // namespace vptd
-#include "vpt_render_flat.cuh" // variant 1 (default): the flat state-machine megakernel
+#include "vpt_render_flat.cuh"  // variant 1: the flat state-machine megakernel
+#include "vpt_render_sched.cuh" // variant 2: flat + warp-level stage scheduling
 namespace vptd {
 
 // ---------------------------------------------------------------- variant 0: the first, nested megakernel (kept for the ncu comparison)
@@ -258,7 +259,8 @@ template <bool TRACE, bool COUNT>
 static void launch_variant(const RenderArgs& args, int variant, int grid_blocks, cudaStream_t stream)
 {
     if (variant == 0) vpt_render_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-    else vpt_render_flat_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else if (variant == 1) vpt_render_flat_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else vpt_render_sched_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
 }
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream)
 {
@@ -270,8 +272,9 @@ template <bool TRACE, bool COUNT>
 static int occupancy_variant(int variant)
 {
     int n = 0;
-    const cudaError_t e = variant == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
-                                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_flat_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0);
+    const cudaError_t e = variant == 0   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
+                          : variant == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_flat_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
+                                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0);
     return e == cudaSuccess ? n : 0;
 }
 int render_blocks_per_sm(int variant, bool trace, bool count)

@@ -24,10 +24,11 @@ struct RenderArgs {
     float* trace_xyz;
     uint32_t* trace_ndraws;
     CountersDev* counters;        // COUNT builds
+    int sched_thresh[4];          // variant 2: lanes needed to run SETUP / DDA / SAMPLE / EVAL in an iteration
 };
 
 cudaError_t upload_cie_table(const float* cie471x3);
-// variant: 0 = nested megakernel (first version), 1 = flat state-machine megakernel (default)
+// variant: 0 = nested megakernel (first version), 1 = flat state machine, 2 = flat + warp-level stage scheduling
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream);
 int render_blocks_per_sm(int variant, bool trace, bool count);
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);

@@ -1,0 +1,227 @@
+// vpt_render_sched.cuh — variant 2: the flat megakernel with WARP-LEVEL STAGE SCHEDULING.
+//
+// Evidence (profiles/r01_dense512_8waves_flat.summary.txt + the per-line source view): in the flat kernel the
+// two hot blocks run with 13-21 active lanes, but the rare-and-long blocks (ray setup: Volume::intersect with
+// its divisions and square roots, HG sampling, camera ray; the trilinear fetch + collision logic) run with
+// 1.6-3 lanes and account for ~45 % of all issued warp instructions — almost every iteration finds at least
+// ONE of the 32 lanes needing them. Here a lane carries an explicit stage
+//     SETUP -> DDA -> SAMPLE -> EVAL (-> SAMPLE | SETUP)
+// and each loop iteration runs a stage only if enough lanes are queued for it (ballot + popc against a per-stage
+// threshold) or it is the most populated one (progress guarantee). Lanes queued for a stage that is skipped
+// simply wait; the arithmetic and its order per lane are unchanged, so results stay bit-identical to variant 1.
+// This is the in-register, in-warp form of wavefront regrouping: no path state ever goes to memory.
+#pragma once
+#include "vpt_render_flat.cuh"
+
+namespace vptd {
+
+enum : int { ST_SETUP = 0, ST_DDA = 1, ST_SAMPLE = 2, ST_EVAL = 3, ST_EXIT = 4 };
+
+template <bool TRACE, bool COUNT>
+__global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(const RenderArgs A)
+{
+    __shared__ float bb[1504];
+    __shared__ double logtab[32];
+    for (int i = threadIdx.x; i < 1504; i += blockDim.x) bb[i] = i < 1500 ? A.bb_table[i] : 0.0f;
+    if (threadIdx.x < 32) logtab[threadIdx.x] = c_logf_table[threadIdx.x];
+    __syncthreads();
+
+    const SceneDev& S = A.scene;
+    const GridDev& G = A.density;
+    const unsigned FULL = 0xffffffffu;
+    const int th_setup = A.sched_thresh[0], th_dda = A.sched_thresh[1], th_sample = A.sched_thresh[2], th_eval = A.sched_thresh[3];
+    Stats st = {0, 0, 0, 0, 0, 0};
+    unsigned long long draws_total = 0;
+    Rng rng; rng.state = 0; rng.draws = 0;
+    CellCache cc, ct;
+    cc.reset(); ct.reset();
+    March m;
+    m.has_seg = false;
+    V3 pos = mk(0, 0, 0), rd = mk(0, 0, 1), L = mk(0, 0, 0);
+    float T_ray = 1.0f;
+    unsigned int depth = 0;
+    bool shadow = false, pixel_open = false;
+    int stage = ST_SETUP, sub = PH_NEXT_PIXEL;
+    unsigned long long j = 0;
+    int x0 = 0, y0 = 0, sx = 0, sy = 0, x = 0, y = 0;
+
+    // the ray left the volume (iterator.next() -> nullopt): back to SETUP
+#define VPT_RAY_FINISHED()                                                                            \
+    do {                                                                                              \
+        if (shadow) sub = PH_AFTER_SHADOW;                                                            \
+        else { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; sub = PH_NEXT_PIXEL; } \
+        stage = ST_SETUP;                                                                             \
+    } while (0)
+
+    for (;;) {
+        const int n_setup = __popc(__ballot_sync(FULL, stage == ST_SETUP)), n_dda = __popc(__ballot_sync(FULL, stage == ST_DDA));
+        const int n_sample = __popc(__ballot_sync(FULL, stage == ST_SAMPLE)), n_eval = __popc(__ballot_sync(FULL, stage == ST_EVAL));
+        const int n_max = max(max(n_setup, n_dda), max(n_sample, n_eval));
+        if (n_max == 0) break; // every lane has exited
+        const bool run_setup = n_setup > 0 && (n_setup >= th_setup || n_setup == n_max);
+        const bool run_dda = n_dda > 0 && (n_dda >= th_dda || n_dda == n_max);
+        const bool run_sample = n_sample > 0 && (n_sample >= th_sample || n_sample == n_max);
+        const bool run_eval = n_eval > 0 && (n_eval >= th_eval || n_eval == n_max);
+
+        // ------------------------------------------------------------ SETUP: pixel / job bookkeeping, ray begin
+        if (run_setup && stage == ST_SETUP) {
+            if (sub == PH_NEXT_PIXEL) {
+                if (pixel_open) { // film(y,x) += (imaging_ratio * L, 1)   worker.cpp:203-204
+                    if (COUNT) ++st.pixel_samples;
+                    if (TRACE) {
+                        const size_t slot = size_t(j) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
+                        A.trace_xyz[slot * 3 + 0] = L.x; A.trace_xyz[slot * 3 + 1] = L.y; A.trace_xyz[slot * 3 + 2] = L.z;
+                        A.trace_ndraws[slot] = rng.draws;
+                    } else {
+                        film_add(A.film + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)) * 4, S.imaging_ratio * L.x, S.imaging_ratio * L.y, S.imaging_ratio * L.z);
+                    }
+                    pixel_open = false;
+                }
+                for (;;) { // next pixel of the job (row-major, worker.cpp:109-110), next job when exhausted
+                    if (++x >= sx) { x = 0; ++y; }
+                    if (y >= sy) {
+                        if (COUNT) draws_total += rng.draws;
+                        j = atomicAdd(A.queue, 1ULL); // TileProvider::next(): m_job_idx.fetch_add(1)
+                        if (j >= A.n_jobs) { stage = ST_EXIT; break; }
+                        uint64_t jid;
+                        if (TRACE) jid = A.trace_jids[j];
+                        else {
+                            const uint64_t k = j / S.ntiles, tile_k = j - k * S.ntiles;
+                            jid = (uint64_t(A.first_wave - 1) + k * A.wave_stride) * S.ntiles + tile_k;
+                        }
+                        const uint64_t tile = jid % S.ntiles;
+                        const int64_t tx0 = int64_t(tile % uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tile / uint64_t(S.ntx)) * S.th;
+                        x0 = int(tx0); y0 = int(ty0);
+                        sx = int(min(S.W - tx0, S.tw)); sy = int(min(S.H - ty0, S.th));
+                        rng.begin_job(S.seed, jid);
+                        x = 0; y = 0;
+                    }
+                    if (S.single_pixel_enabled && (int64_t(x0 + x) != S.single_pixel_x || int64_t(y0 + y) != S.single_pixel_y)) continue;
+                    break;
+                }
+                if (stage != ST_EXIT) { // camera path start   worker.cpp:121-128, camera.hpp:14-23
+                    const float j0 = rng.uniform(), j1 = rng.uniform();
+                    const float jm = S.use_jitter ? 0.5f : 0.0f;
+                    const float rx = (float(x0 + x) + 0.5f) + j0 * jm, ry = (float(y0 + y) + 0.5f) + j1 * jm;
+                    rd = normalized(mk(sum3(S.cam_m[0] * rx, S.cam_m[1] * ry, S.cam_m[2] * 0.0f) + S.cam_t[0],
+                                       sum3(S.cam_m[3] * rx, S.cam_m[4] * ry, S.cam_m[5] * 0.0f) + S.cam_t[1],
+                                       sum3(S.cam_m[6] * rx, S.cam_m[7] * ry, S.cam_m[8] * 0.0f) + S.cam_t[2]));
+                    pos = mk(S.cam_pos[0], S.cam_pos[1], S.cam_pos[2]);
+                    L = mk(0.0f, 0.0f, 0.0f);
+                    depth = 0; shadow = false; pixel_open = true;
+                }
+            } else if (sub == PH_BEGIN_SHADOW) { // sample_Ld   worker.cpp:59-66
+                shadow = true; T_ray = 1.0f;
+                if (COUNT) ++st.shadow_rays;
+            } else { // PH_AFTER_SHADOW: worker.cpp:88-89 then :175-183
+                const V3 wi = mk(S.dist_wi[0], S.dist_wi[1], S.dist_wi[2]);
+                const float k = henyey_greenstein(dot3(rd, wi), S.g) * T_ray;
+                L.x += k * S.dist_Li[0]; L.y += k * S.dist_Li[1]; L.z += k * S.dist_Li[2];
+                const float u0 = rng.uniform(), u1 = rng.uniform();
+                rd = sample_henyey_greenstein(rd, u0, u1, S.g);
+                shadow = false;
+                depth += 2; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
+            }
+            if (stage != ST_EXIT) {
+                if (!shadow && depth >= S.max_depth) { // bounce loop out of depth: not terminated -> infinite light (:198-200)
+                    L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2];
+                    sub = PH_NEXT_PIXEL;
+                } else {
+                    const V3 dir = shadow ? mk(S.dist_wi[0], S.dist_wi[1], S.dist_wi[2]) : rd;
+                    bool ray_done;
+                    if (flat_begin_ray<COUNT>(m, G, cc, pos, dir, ray_done, st)) {
+                        if (ray_done) VPT_RAY_FINISHED();
+                        else stage = ST_DDA;
+                    } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
+                    else { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; sub = PH_NEXT_PIXEL; }
+                }
+            }
+        }
+
+        // ------------------------------------------------------------ DDA: one HDDA step   volume.cpp:53-71
+        if (run_dda && stage == ST_DDA) {
+            bool closed;
+            if (!hdda_step(m)) { m.seg_t1 = m.t1; closed = true; }
+            else {
+                const V3 p = m.at(m.t0 + 1.0001f);
+                hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
+                m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
+                if (COUNT) ++st.majorant_fetches;
+                closed = m.majorant != m.seg_dmaj;
+                if (closed) m.seg_t1 = m.t0;
+            }
+            if (closed) {
+                if (m.seg_dmaj > 0.0f) stage = ST_SAMPLE;
+                else if (m.t0 >= m.t1) VPT_RAY_FINISHED();         // empty segment dropped, iterator.next() -> nullopt
+                else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
+            }
+        }
+        // ------------------------------------------------------------ SAMPLE: one free flight   majorant_transmittance_sampler.cpp:41-77
+        if (run_sample && stage == ST_SAMPLE) {
+            const float sigma_maj = m.seg_dmaj * S.sigma_t;
+            const float dt_m = -vptm::logf_exact(1.0f - rng.uniform(), logtab) / sigma_maj;
+            const float t = m.seg_t0 + dt_m / m.scale;
+            if (t < m.seg_t1) { m.seg_t0 = t; stage = ST_EVAL; }
+            else if (m.t0 >= m.t1) VPT_RAY_FINISHED();             // overshoot: segment dropped, iterator.next()
+            else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; stage = ST_DDA; }
+        }
+        // ------------------------------------------------------------ EVAL: trilinear density + collision   worker.cpp:68-84,148-188
+        if (run_eval && stage == ST_EVAL) {
+            const V3 p = m.at(m.seg_t0);
+            if (COUNT) ++st.density_evals;
+            const float density = trilinear_cached(G, cc, p.x, p.y, p.z);
+            stage = ST_SAMPLE;
+            if (density > 0.0f) {
+                const float sigma_maj = m.seg_dmaj * S.sigma_t;
+                if (shadow) { // ratio tracking + Russian roulette
+                    const float sigma_n = fmaxf(0.0f, sigma_maj - S.sigma_t * density);
+                    T_ray *= sigma_n / sigma_maj;
+                    if (T_ray <= 0.05f) {
+                        if (rng.uniform() < 0.75f) T_ray = 0.0f;
+                        else T_ray /= 0.25f;
+                    }
+                    if (T_ray <= 0.0f) { T_ray = 0.0f; sub = PH_AFTER_SHADOW; stage = ST_SETUP; }
+                } else {
+                    const V3 point = index_to_world(G, p);
+                    const float p_a = (S.sigma_a * density) / sigma_maj;
+                    const float p_s = (S.sigma_s * density) / sigma_maj;
+                    const float p_n = fmaxf(1.0f - p_a - p_s, 0.0f);
+                    if (S.has_temperature) {
+                        const V3 tc = world_to_index(A.temperature, point);
+                        if (COUNT) ++st.temperature_evals;
+                        const float temp_adim = trilinear_cached(A.temperature, ct, tc.x, tc.y, tc.z);
+                        const float temp_K = temp_adim * S.temperature_scale + S.temperature_offset;
+                        const V3 e = blackbody_xyz(bb, temp_K);
+                        const float k = p_a * S.le_scale;
+                        L.x += k * e.x; L.y += k * e.y; L.z += k * e.z;
+                    }
+                    float u = rng.uniform() * (((0.0f + p_n) + p_a) + p_s); // sample_discrete  random.hpp:31-47
+                    u -= p_n;
+                    if (u > 0.0f) {
+                        u -= p_a;
+                        stage = ST_SETUP;
+                        if (u <= 0.0f) sub = PH_NEXT_PIXEL; // absorption: terminated, no infinite light
+                        else {                               // scatter (also the fallback choice)
+                            if (COUNT) ++st.scatter_events;
+                            pos = point;
+                            if (S.dist_light_on) sub = PH_BEGIN_SHADOW;
+                            else { T_ray = 0.0f; sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
+                        }
+                    }
+                }
+            }
+        }
+    }
+#undef VPT_RAY_FINISHED
+    if (COUNT) {
+        atomicAdd(&A.counters->pixel_samples, (unsigned long long)st.pixel_samples);
+        atomicAdd(&A.counters->density_evals, (unsigned long long)st.density_evals);
+        atomicAdd(&A.counters->temperature_evals, (unsigned long long)st.temperature_evals);
+        atomicAdd(&A.counters->majorant_fetches, (unsigned long long)st.majorant_fetches);
+        atomicAdd(&A.counters->rng_draws, draws_total);
+        atomicAdd(&A.counters->scatter_events, (unsigned long long)st.scatter_events);
+        atomicAdd(&A.counters->shadow_rays, (unsigned long long)st.shadow_rays);
+    }
+}
+
+} // namespace vptd

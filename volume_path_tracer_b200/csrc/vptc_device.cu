@@ -1,6 +1,7 @@
 // vptc_device.cu — the device-facing entry points of include/vptc.h: context, volume staging, render,
 // parity hooks. Plain CUDA runtime; no torch types cross this boundary.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
@@ -40,7 +41,8 @@ struct vptc_ctx {
     unsigned long long* queue = nullptr;
     CountersDev* counters = nullptr;
     bool count = false;
-    int variant = 1; // render kernel variant (vptc_set_kernel_variant)
+    int variant = 2; // render kernel variant (vptc_set_kernel_variant)
+    int sched_thresh[4] = {12, 8, 8, 12};
     float last_ms = 0.0f;
     vptc_counters last_counters{};
     int num_sms = 0;
@@ -105,6 +107,7 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     A.bb_table = ctx->bb_table;
     A.queue = ctx->queue;
     A.counters = ctx->counters;
+    for (int i = 0; i < 4; ++i) A.sched_thresh[i] = ctx->sched_thresh[i];
     CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
     const int per_sm = render_blocks_per_sm(ctx->variant, trace, ctx->count);
@@ -158,7 +161,9 @@ int vptc_create(vptc_ctx** out, int device)
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
     CU(upload_cie_table(vpt_host::cie_table()));
-    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::atoi(v) == 0 ? 0 : 1;
+    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(2, std::max(0, std::atoi(v)));
+    if (const char* v = std::getenv("VPT_SCHED_THRESH")) // "setup,dda,sample,eval" lanes (tuning aid)
+        std::sscanf(v, "%d,%d,%d,%d", &ctx->sched_thresh[0], &ctx->sched_thresh[1], &ctx->sched_thresh[2], &ctx->sched_thresh[3]);
     *out = c.release();
     return VPTC_OK;
 }
@@ -259,7 +264,7 @@ int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 int vptc_set_kernel_variant(vptc_ctx* ctx, int variant)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: ctx is null");
-    if (variant != 0 && variant != 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested megakernel) or 1 (flat megakernel)");
+    if (variant < 0 || variant > 2) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat) or 2 (flat + stage scheduling)");
     ctx->variant = variant;
     return VPTC_OK;
 }
