@@ -43,11 +43,11 @@ METRIC, UNIT = "pixel_samples_per_sec", "pixel-samples/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="dense512", help="fire | fire_lowscattering | wdas_cloud | dense512 | wdas_cloud_4k")
-    ap.add_argument("--waves-per-step", type=int, default=8)
+    ap.add_argument("--waves-per-step", type=int, default=32)
     ap.add_argument("--volume-scale", type=float, default=1.0, help="resolution factor of the synthetic volume (1 = the named shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
@@ -312,7 +312,7 @@ def run_ours(args):
                     "note": "vptc_render: scene POD (200 B) in, float4 film out and accumulated on the host; the volume is staged to HBM once, "
                             "like the reference loads its grids once"},
             "gpu_launches": K,
-            "kernel": "vpt_render_kernel (1 launch per step per GPU)",
+            "kernel": "vpt_render_sched_kernel (variant 2; 1 launch per step per GPU)",
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "kernel_ms": k_ms,
                          "algorithmic_bytes_per_pixel_sample": alg_bytes_per_sample,
