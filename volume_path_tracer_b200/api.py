@@ -19,7 +19,7 @@ from pathlib import Path
 import numpy as np
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "libvptcuda.so"
+LIB_PATH = Path(os.environ["VPT_LIBVPTCUDA"]) if os.environ.get("VPT_LIBVPTCUDA") else _PKG / "libvptcuda.so"  # env: development builds only
 
 
 # ---------------------------------------------------------------- POD structs (include/vptc.h)

@@ -197,6 +197,22 @@ __device__ __forceinline__ bool hdda_step(March& m)
     return m.t0 <= m.t1;
 }
 
+// hdda_step without the three-way axis branch (the x / y / z arms diverge inside a warp): same operations on the
+// selected axis, selected with predicated moves.
+__device__ __forceinline__ bool hdda_step_bf(March& m)
+{
+    const bool ax = m.nx < m.ny && m.nx < m.nz, ay = !ax && m.ny < m.nz, az = !ax && !ay;
+    float n = ax ? m.nx : (ay ? m.ny : m.nz);
+    const float inv = ax ? m.ix : (ay ? m.iy : m.iz);
+    if (n <= m.t0) n += m.t0 - 0.999999f * n + 1.0e-6f;
+    m.t0 = n;
+    const float n2 = n + float(m.dim) * fabsf(inv);
+    const int step = inv > 0.0f ? m.dim : -m.dim;
+    m.nx = ax ? n2 : m.nx; m.ny = ay ? n2 : m.ny; m.nz = az ? n2 : m.nz;
+    m.vx += ax ? step : 0; m.vy += ay ? step : 0; m.vz += az ? step : 0;
+    return m.t0 <= m.t1;
+}
+
 // Volume::intersect + RayMajorantIterator ctor   src/volume.cpp:78-98, NV/math/Ray.h:64-74,258-268,398-424
 __device__ __forceinline__ bool march_begin(March& m, const GridDev& G, V3 o, V3 d)
 {

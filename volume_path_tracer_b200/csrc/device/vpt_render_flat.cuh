@@ -34,7 +34,7 @@ __device__ __forceinline__ uint32_t cell_code_cached(const GridDev& G, CellCache
     if (unsigned(cx) >= unsigned(G.cell_dim[0]) || unsigned(cy) >= unsigned(G.cell_dim[1]) || unsigned(cz) >= unsigned(G.cell_dim[2]))
         code = CELL_KIND_TILE | (2u << CELL_DIM_SHIFT);
     else
-        code = __ldg(&G.cells[(size_t(cx) * size_t(G.cell_dim[1]) + size_t(cy)) * size_t(G.cell_dim[2]) + size_t(cz)]);
+        code = __ldg(&G.cells[(cx * G.cell_dim[1] + cy) * G.cell_dim[2] + cz]); // < 2^27 cells (bake.cpp): 32-bit index
     cc.cx = cx; cc.cy = cy; cc.cz = cz; cc.code = code;
     return code;
 }

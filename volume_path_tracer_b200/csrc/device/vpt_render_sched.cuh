@@ -15,10 +15,14 @@
 
 namespace vptd {
 
-enum : int { ST_SETUP = 0, ST_DDA = 1, ST_SAMPLE = 2, ST_EVAL = 3, ST_EXIT = 4 };
+#ifndef VPT_SCHED_MIN_BLOCKS
+#define VPT_SCHED_MIN_BLOCKS 5 // resident 128-thread blocks per SM the register allocation must allow
+#endif
+
+enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
 
 template <bool TRACE, bool COUNT>
-__global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(const RenderArgs A)
+__global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_render_sched_kernel(const RenderArgs A)
 {
     __shared__ float bb[1504];
     __shared__ double logtab[32];
@@ -29,7 +33,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(con
     const SceneDev& S = A.scene;
     const GridDev& G = A.density;
     const unsigned FULL = 0xffffffffu;
-    const int th_setup = A.sched_thresh[0], th_dda = A.sched_thresh[1], th_sample = A.sched_thresh[2], th_eval = A.sched_thresh[3];
+    const int th_setup = max(1, A.sched_thresh[0]), th_hot = max(1, A.sched_thresh[1]), th_eval = max(1, A.sched_thresh[3]);
     Stats st = {0, 0, 0, 0, 0, 0};
     unsigned long long draws_total = 0;
     Rng rng; rng.state = 0; rng.draws = 0;
@@ -37,8 +41,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(con
     cc.reset(); ct.reset();
     March m;
     m.has_seg = false;
-    V3 pos = mk(0, 0, 0), rd = mk(0, 0, 1), L = mk(0, 0, 0);
-    float T_ray = 1.0f;
+    V3 pos = mk(0, 0, 0), rd = mk(0, 0, 1), L = mk(0, 0, 0), pos_idx = mk(0, 0, 0);
+    float T_ray = 1.0f, pend_u = 0.0f;
     unsigned int depth = 0;
     bool shadow = false, pixel_open = false;
     int stage = ST_SETUP, sub = PH_NEXT_PIXEL;
@@ -54,14 +58,13 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(con
     } while (0)
 
     for (;;) {
-        const int n_setup = __popc(__ballot_sync(FULL, stage == ST_SETUP)), n_dda = __popc(__ballot_sync(FULL, stage == ST_DDA));
-        const int n_sample = __popc(__ballot_sync(FULL, stage == ST_SAMPLE)), n_eval = __popc(__ballot_sync(FULL, stage == ST_EVAL));
-        const int n_max = max(max(n_setup, n_dda), max(n_sample, n_eval));
+        const int n_setup = __popc(__ballot_sync(FULL, stage == ST_SETUP)), n_hot = __popc(__ballot_sync(FULL, stage == ST_HOT));
+        const int n_eval = __popc(__ballot_sync(FULL, stage == ST_EVAL));
+        const int n_max = max(n_setup, max(n_hot, n_eval));
         if (n_max == 0) break; // every lane has exited
-        const bool run_setup = n_setup > 0 && (n_setup >= th_setup || n_setup == n_max);
-        const bool run_dda = n_dda > 0 && (n_dda >= th_dda || n_dda == n_max);
-        const bool run_sample = n_sample > 0 && (n_sample >= th_sample || n_sample == n_max);
-        const bool run_eval = n_eval > 0 && (n_eval >= th_eval || n_eval == n_max);
+        const bool run_setup = n_setup >= th_setup || n_setup == n_max;
+        const bool run_hot = n_hot >= th_hot || n_hot == n_max;
+        const bool run_eval = n_eval >= th_eval || n_eval == n_max;
 
         // ------------------------------------------------------------ SETUP: pixel / job bookkeeping, ray begin
         if (run_setup && stage == ST_SETUP) {
@@ -131,48 +134,66 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(con
                     bool ray_done;
                     if (flat_begin_ray<COUNT>(m, G, cc, pos, dir, ray_done, st)) {
                         if (ray_done) VPT_RAY_FINISHED();
-                        else stage = ST_DDA;
+                        else stage = ST_HOT;
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
                     else { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; sub = PH_NEXT_PIXEL; }
                 }
             }
         }
 
-        // ------------------------------------------------------------ DDA: one HDDA step   volume.cpp:53-71
-        if (run_dda && stage == ST_DDA) {
-            bool closed;
-            if (!hdda_step(m)) { m.seg_t1 = m.t1; closed = true; }
-            else {
-                const V3 p = m.at(m.t0 + 1.0001f);
-                hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
-                m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
-                if (COUNT) ++st.majorant_fetches;
-                closed = m.majorant != m.seg_dmaj;
-                if (closed) m.seg_t1 = m.t0;
+        // ------------------------------------------------------------ HOT: one HDDA step and/or one free-flight draw
+        if (run_hot && stage == ST_HOT) {
+            if (!m.has_seg) { // RayMajorantIterator::next, one step   volume.cpp:53-71
+                bool closed;
+                if (!hdda_step_bf(m)) { m.seg_t1 = m.t1; closed = true; }
+                else {
+                    const V3 p = m.at(m.t0 + 1.0001f);
+                    hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
+                    m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
+                    if (COUNT) ++st.majorant_fetches;
+                    closed = m.majorant != m.seg_dmaj;
+                    if (closed) m.seg_t1 = m.t0;
+                }
+                if (closed) {
+                    if (m.seg_dmaj > 0.0f) m.has_seg = true;
+                    else if (m.t0 >= m.t1) VPT_RAY_FINISHED();         // empty segment dropped, iterator.next() -> nullopt
+                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
+                }
             }
-            if (closed) {
-                if (m.seg_dmaj > 0.0f) stage = ST_SAMPLE;
-                else if (m.t0 >= m.t1) VPT_RAY_FINISHED();         // empty segment dropped, iterator.next() -> nullopt
-                else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
+            if (m.has_seg && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
+                pend_u = rng.uniform();
+                // ~85 % of the draws overshoot the segment. Only the DECISION `t < seg.t1` matters then, not t itself, so
+                // a conservative test with the SFU approximations (MUFU.LG2 / RCP, error margins far above their
+                // documented bounds) settles the clear cases; everything else — the hits and the ~0.1 % near the
+                // boundary — goes to EVAL, which evaluates t exactly (glibc-exact logf, IEEE divisions) and decides.
+                const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
+                const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
+                if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
+                    m.has_seg = false;
+                    if (m.t0 >= m.t1) VPT_RAY_FINISHED();
+                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
+                } else stage = ST_EVAL;
             }
-        }
-        // ------------------------------------------------------------ SAMPLE: one free flight   majorant_transmittance_sampler.cpp:41-77
-        if (run_sample && stage == ST_SAMPLE) {
-            const float sigma_maj = m.seg_dmaj * S.sigma_t;
-            const float dt_m = -vptm::logf_exact(1.0f - rng.uniform(), logtab) / sigma_maj;
-            const float t = m.seg_t0 + dt_m / m.scale;
-            if (t < m.seg_t1) { m.seg_t0 = t; stage = ST_EVAL; }
-            else if (m.t0 >= m.t1) VPT_RAY_FINISHED();             // overshoot: segment dropped, iterator.next()
-            else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; stage = ST_DDA; }
         }
         // ------------------------------------------------------------ EVAL: trilinear density + collision   worker.cpp:68-84,148-188
         if (run_eval && stage == ST_EVAL) {
-            const V3 p = m.at(m.seg_t0);
-            if (COUNT) ++st.density_evals;
-            const float density = trilinear_cached(G, cc, p.x, p.y, p.z);
-            stage = ST_SAMPLE;
+            const float sigma_maj = m.seg_dmaj * S.sigma_t;
+            const float dt_m = -vptm::logf_exact(1.0f - pend_u, logtab) / sigma_maj; // sample_exponential  random.hpp:19-22
+            const float t = m.seg_t0 + dt_m / m.scale;
+            stage = ST_HOT;
+            float density = 0.0f;
+            if (t < m.seg_t1) {
+                m.seg_t0 = t;
+                const V3 p = m.at(t);
+                if (COUNT) ++st.density_evals;
+                density = trilinear_cached(G, cc, p.x, p.y, p.z);
+                if (density > 0.0f) pos_idx = p;
+            } else { // overshoot after all: segment dropped, iterator.next()
+                m.has_seg = false;
+                if (m.t0 >= m.t1) VPT_RAY_FINISHED();
+                else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
+            }
             if (density > 0.0f) {
-                const float sigma_maj = m.seg_dmaj * S.sigma_t;
                 if (shadow) { // ratio tracking + Russian roulette
                     const float sigma_n = fmaxf(0.0f, sigma_maj - S.sigma_t * density);
                     T_ray *= sigma_n / sigma_maj;
@@ -182,7 +203,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS) vpt_render_sched_kernel(con
                     }
                     if (T_ray <= 0.0f) { T_ray = 0.0f; sub = PH_AFTER_SHADOW; stage = ST_SETUP; }
                 } else {
-                    const V3 point = index_to_world(G, p);
+                    const V3 point = index_to_world(G, pos_idx);
                     const float p_a = (S.sigma_a * density) / sigma_maj;
                     const float p_s = (S.sigma_s * density) / sigma_maj;
                     const float p_n = fmaxf(1.0f - p_a - p_s, 0.0f);
