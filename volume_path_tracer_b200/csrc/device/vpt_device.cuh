@@ -214,15 +214,30 @@ __device__ __forceinline__ bool hdda_step_bf(March& m)
 }
 
 // Volume::intersect + RayMajorantIterator ctor   src/volume.cpp:78-98, NV/math/Ray.h:64-74,258-268,398-424
-__device__ __forceinline__ bool march_begin(March& m, const GridDev& G, V3 o, V3 d)
+// The direction-only part of Ray::worldToIndexF + the iterator's idx_to_world scale: constant for all shadow rays
+// of a scene (one distant light), so the kernels evaluate it once per block for those.
+struct RayDir { float dx, dy, dz, ix, iy, iz, length, scale; };
+__device__ __forceinline__ RayDir make_ray_dir(const GridDev& G, V3 d)
+{
+    RayDir r;
+    const V3 di = mat3(G.invMat, d);
+    r.length = sqrtf(di.x * di.x + di.y * di.y + di.z * di.z);
+    const float invLength = 1.0f / r.length;
+    r.dx = invLength * di.x; r.dy = invLength * di.y; r.dz = invLength * di.z;
+    r.ix = 1.0f / r.dx; r.iy = 1.0f / r.dy; r.iz = 1.0f / r.dz;
+    // m_scale = 1 / density.worldToIndexDirF(ray.dir()).length(), with the INDEX-space direction (volume.cpp:91)
+    const V3 q = mat3(G.invMat, mk(r.dx, r.dy, r.dz));
+    r.scale = 1.0f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
+    return r;
+}
+// Everything of march_begin except the HDDA init (the caller picks the cached or uncached getDim lookup).
+__device__ __forceinline__ bool march_begin_dir(March& m, const GridDev& G, V3 o, const RayDir& r)
 {
     const V3 eye = world_to_index(G, o);
-    const V3 di = mat3(G.invMat, d);
-    const float length = sqrtf(di.x * di.x + di.y * di.y + di.z * di.z), invLength = 1.0f / length;
     m.ex = eye.x; m.ey = eye.y; m.ez = eye.z;
-    m.dx = invLength * di.x; m.dy = invLength * di.y; m.dz = invLength * di.z;
-    m.ix = 1.0f / m.dx; m.iy = 1.0f / m.dy; m.iz = 1.0f / m.dz;
-    float t0 = length * 1e-5f, t1 = FLT_MAX; // Delta<float>, host Maximum<float>
+    m.dx = r.dx; m.dy = r.dy; m.dz = r.dz;
+    m.ix = r.ix; m.iy = r.iy; m.iz = r.iz;
+    float t0 = r.length * 1e-5f, t1 = FLT_MAX; // Delta<float>, host Maximum<float>
     // clip against indexBBox with max + 1
     {
         float a = float(G.bbox_min[0]), b = float(G.bbox_max[0] + 1);
@@ -248,11 +263,14 @@ __device__ __forceinline__ bool march_begin(March& m, const GridDev& G, V3 o, V3
         if (t0 > t1) return false;
     }
     m.t0 = t0; m.t1 = t1;
-    // m_scale = 1 / density.worldToIndexDirF(ray.dir()).length(), with the INDEX-space direction (volume.cpp:91)
-    const V3 q = mat3(G.invMat, mk(m.dx, m.dy, m.dz));
-    m.scale = 1.0f / sqrtf(q.x * q.x + q.y * q.y + q.z * q.z);
+    m.scale = r.scale;
     m.majorant = __int_as_float(0x7fc00000); // NaN: not fetched yet
     m.has_seg = false;
+    return true;
+}
+__device__ __forceinline__ bool march_begin(March& m, const GridDev& G, V3 o, V3 d)
+{
+    if (!march_begin_dir(m, G, o, make_ray_dir(G, d))) return false;
     const V3 s = m.at(m.t0);
     hdda_init(m, hdda_dim(G, int(floorf(s.x)), int(floorf(s.y)), int(floorf(s.z))));
     return true;

@@ -83,12 +83,9 @@ __device__ __forceinline__ float trilinear_cached(const GridDev& G, CellCache& c
 
 enum : int { PH_MARCH = 0, PH_NEXT_PIXEL = 1, PH_BEGIN_SHADOW = 2, PH_AFTER_SHADOW = 3, PH_EXIT = 4 };
 
-// march_begin of vpt_device.cuh + the iterator's first majorant fetch + the first segment start.
-// Returns false when the ray misses the index bbox (Volume::intersect -> nullopt) — no majorant is fetched then.
 template <bool COUNT>
-__device__ __forceinline__ bool flat_begin_ray(March& m, const GridDev& G, CellCache& cc, V3 o, V3 d, bool& ray_done, Stats& st)
+__device__ __forceinline__ bool flat_first_segment(March& m, const GridDev& G, CellCache& cc, bool& ray_done, Stats& st)
 {
-    if (!march_begin(m, G, o, d)) return false;
     ray_done = false;
     // RayMajorantIterator::next, first call: `if (time >= maxTime) return nullopt` comes BEFORE the first fetch
     if (m.t0 >= m.t1) { ray_done = true; return true; }
@@ -96,6 +93,23 @@ __device__ __forceinline__ bool flat_begin_ray(March& m, const GridDev& G, CellC
     if (COUNT) ++st.majorant_fetches;
     m.seg_t0 = m.t0; m.seg_dmaj = m.majorant;
     return true;
+}
+// march_begin of vpt_device.cuh + the iterator's first majorant fetch + the first segment start.
+// Returns false when the ray misses the index bbox (Volume::intersect -> nullopt) — no majorant is fetched then.
+template <bool COUNT>
+__device__ __forceinline__ bool flat_begin_ray(March& m, const GridDev& G, CellCache& cc, V3 o, V3 d, bool& ray_done, Stats& st)
+{
+    if (!march_begin(m, G, o, d)) return false;
+    return flat_first_segment<COUNT>(m, G, cc, ray_done, st);
+}
+// Same with a precomputed direction (shadow rays) and the cached getDim lookup.
+template <bool COUNT>
+__device__ __forceinline__ bool flat_begin_ray_dir(March& m, const GridDev& G, CellCache& cc, V3 o, const RayDir& r, bool& ray_done, Stats& st)
+{
+    if (!march_begin_dir(m, G, o, r)) return false;
+    const V3 s = m.at(m.t0);
+    hdda_init(m, dim_of_code(cell_code_cached(G, cc, int(floorf(s.x)), int(floorf(s.y)), int(floorf(s.z)))));
+    return flat_first_segment<COUNT>(m, G, cc, ray_done, st);
 }
 
 template <bool TRACE, bool COUNT>

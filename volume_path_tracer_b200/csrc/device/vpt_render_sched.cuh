@@ -28,6 +28,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     __shared__ double logtab[32];
     for (int i = threadIdx.x; i < 1504; i += blockDim.x) bb[i] = i < 1500 ? A.bb_table[i] : 0.0f;
     if (threadIdx.x < 32) logtab[threadIdx.x] = c_logf_table[threadIdx.x];
+    __shared__ RayDir shadow_dir; // every shadow ray points at the one distant light: direction terms once per block
+    if (threadIdx.x == 32) shadow_dir = make_ray_dir(A.density, mk(A.scene.dist_wi[0], A.scene.dist_wi[1], A.scene.dist_wi[2]));
     __syncthreads();
 
     const SceneDev& S = A.scene;
@@ -130,9 +132,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2];
                     sub = PH_NEXT_PIXEL;
                 } else {
-                    const V3 dir = shadow ? mk(S.dist_wi[0], S.dist_wi[1], S.dist_wi[2]) : rd;
                     bool ray_done;
-                    if (flat_begin_ray<COUNT>(m, G, cc, pos, dir, ray_done, st)) {
+                    const RayDir rdir = shadow ? shadow_dir : make_ray_dir(G, rd);
+                    if (flat_begin_ray_dir<COUNT>(m, G, cc, pos, rdir, ray_done, st)) {
                         if (ray_done) VPT_RAY_FINISHED();
                         else stage = ST_HOT;
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
