@@ -1,12 +1,14 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, bench line, ncu launch list + one full capture of the render kernel.
+# One GPU-box visit: smoke, parity tests, both bench arms, ncu launch list of the bench command, one full capture
+# of the render kernel (each ncu run only after the same command exited 0 without ncu).
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
-python bench.py --steps 6 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json
-NCU_CMD="python bench.py --steps 1 --warmup 3 --waves-per-step 1 --no-cpu-baseline"
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/smoke.log
+python -m pytest tests -m gpu -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+tail -3 gpurun_out/pytest_gpu.log
+python bench.py --impl reference > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench reference rc=$?"
+python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json
+NCU_CMD="python bench.py --steps 2 --warmup 3 --waves-per-step 8 --no-cpu-baseline"
 $NCU_CMD > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches.csv $NCU_CMD > gpurun_out/ncu_launches.log 2>&1
-$NCU_CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:vpt_render_kernel -s 3 -c 1 -f -o gpurun_out/prof $NCU_CMD > gpurun_out/ncu_full.log 2>&1
-ls -la gpurun_out
+ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $NCU_CMD > gpurun_out/ncu_launches.log 2>&1
+VARIANTS=2 bash tools/gpu_ncu.sh dense512 16 1.0 r01_dense512_sched_full
+ls -la gpurun_out | tail -30
