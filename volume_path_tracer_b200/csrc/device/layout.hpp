@@ -14,8 +14,7 @@
 // Level 2 "bricks": per leaf 9x9x9 floats = the 8^3 voxels plus a +1 apron in x, y, z (values read
 //   through getValue at bake time, so whatever lies beyond the leaf — another leaf, a tile, background —
 //   is already folded in). A trilinear stencil whose base voxel lies in a leaf touches exactly one brick.
-//   Brick stride is padded to 736 floats (2944 B = 92 sectors of 32 B). On the device the apron bricks are normally
-//   expanded once into "stencil bricks" (below): one 32-byte sector per trilinear fetch instead of 4-8.
+//   Brick stride is padded to 736 floats (2944 B = 92 sectors of 32 B).
 #pragma once
 #include <cstdint>
 
@@ -32,11 +31,6 @@ struct Slot { uint32_t code; float majorant; }; // 8 bytes, loaded as one 64-bit
 
 constexpr int BRICK_EDGE = 9;
 constexpr int BRICK_STRIDE = 736; // floats; >= 9^3 = 729
-// Stencil bricks: for every base voxel of a leaf the 8 corner values of its trilinear cell, contiguous and 32-byte
-// aligned (v000 v001 v010 v011 | v100 v101 v110 v111, z fastest) = exactly ONE 32-byte sector per trilinear fetch,
-// read as two 16-byte loads. 8x the voxel count in bytes (16 KB per leaf), expanded on the device from the apron
-// bricks at set_volume time when HBM allows (it does for every BASELINE configuration: 4.3 GB dense 512^3, 27 GB cloud).
-constexpr int STENCIL_STRIDE = 4096; // floats per leaf
 
 struct GridDev {
     // NanoVDB Map, float members verbatim (NV/NanoVDB.h:1375-1381)
@@ -50,9 +44,7 @@ struct GridDev {
     const float* tile_value;          // [nTiles] value getValue returns inside the tile
     const float* tile_majorant;       // [nTiles] active ? value : 0        (volume.cpp:28-34)
     const float* bricks;              // [nBricks * BRICK_STRIDE]
-    uint32_t n_lower, n_bricks, n_tiles;
-    uint32_t stencil_bricks;          // 0: `bricks` = 9^3 apron bricks (BRICK_STRIDE floats each);
-                                      // 1: `bricks` = 8^3 x 8-corner stencil bricks (STENCIL_STRIDE floats each)
+    uint32_t n_lower, n_bricks, n_tiles, pad_;
 };
 
 // vpt::Configuration flattened to what the kernels read, plus host-precomputed constants.

@@ -91,25 +91,7 @@ __device__ __forceinline__ float value_at(const GridDev& G, int x, int y, int z)
     if (c & CELL_KIND_TILE) return __ldg(&G.tile_value[c & CELL_INDEX_MASK]);
     const Slot s = load_slot(G, slot_index(c, x, y, z));
     if (s.code & SLOT_KIND_TILE) return __ldg(&G.tile_value[s.code & SLOT_INDEX_MASK]);
-    if (G.stencil_bricks) return __ldg(&G.bricks[size_t(s.code) * STENCIL_STRIDE + size_t(((x & 7) << 6 | (y & 7) << 3 | (z & 7)) * 8)]);
     return __ldg(&G.bricks[size_t(s.code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7)]);
-}
-// The 8 corners of the trilinear cell whose base voxel (x, y, z) lies in leaf `code`.
-__device__ __forceinline__ void brick_corners(const GridDev& G, uint32_t code, int x, int y, int z, float& v000, float& v001, float& v010,
-                                              float& v011, float& v100, float& v101, float& v110, float& v111)
-{
-    if (G.stencil_bricks) { // one aligned 32-byte sector
-        const float4* b = reinterpret_cast<const float4*>(G.bricks + size_t(code) * STENCIL_STRIDE) + ((x & 7) << 6 | (y & 7) << 3 | (z & 7)) * 2;
-        const float4 lo = __ldg(b), hi = __ldg(b + 1);
-        v000 = lo.x; v001 = lo.y; v010 = lo.z; v011 = lo.w;
-        v100 = hi.x; v101 = hi.y; v110 = hi.z; v111 = hi.w;
-    } else {
-        const float* b = G.bricks + size_t(code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7);
-        v000 = __ldg(b);      v001 = __ldg(b + 1);
-        v010 = __ldg(b + 9);  v011 = __ldg(b + 10);
-        v100 = __ldg(b + 81); v101 = __ldg(b + 82);
-        v110 = __ldg(b + 90); v111 = __ldg(b + 91);
-    }
 }
 // SampleFromVoxels<Acc,1>::operator()(Vec3f)   NV/math/SampleFromVoxels.h:62-69,202-242
 __device__ __forceinline__ float trilinear(const GridDev& G, float px, float py, float pz)
@@ -123,7 +105,11 @@ __device__ __forceinline__ float trilinear(const GridDev& G, float px, float py,
     if (!(c & CELL_KIND_TILE)) {
         const Slot s = load_slot(G, slot_index(c, x, y, z));
         if (!(s.code & SLOT_KIND_TILE)) { // base voxel in a leaf: the 9^3 apron brick holds all 8 corners
-            brick_corners(G, s.code, x, y, z, v000, v001, v010, v011, v100, v101, v110, v111);
+            const float* b = G.bricks + size_t(s.code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7);
+            v000 = __ldg(b);      v001 = __ldg(b + 1);
+            v010 = __ldg(b + 9);  v011 = __ldg(b + 10);
+            v100 = __ldg(b + 81); v101 = __ldg(b + 82);
+            v110 = __ldg(b + 90); v111 = __ldg(b + 91);
             fast = true;
         }
     }

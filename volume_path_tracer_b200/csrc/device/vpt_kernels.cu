@@ -252,27 +252,6 @@ __global__ void vpt_resolve_kernel(const float4* film, size_t n, uint8_t* rgb)
     }
 }
 
-// ---------------------------------------------------------------- bake: apron bricks -> stencil bricks (layout.hpp)
-// One block per leaf, one thread per base voxel: gathers the 8 corners from the 9^3 apron brick and writes one
-// 32-byte entry (two coalesced 16-byte stores per thread).
-__global__ void __launch_bounds__(512) vpt_expand_bricks_kernel(const float* __restrict__ apron, float4* __restrict__ stencil, uint32_t first_brick)
-{
-    const size_t brick = size_t(blockIdx.x) + first_brick;
-    const int n = threadIdx.x, x = n >> 6, y = (n >> 3) & 7, z = n & 7;
-    const float* b = apron + brick * BRICK_STRIDE + (x * 9 + y) * 9 + z;
-    float4* o = stencil + (brick * 512 + n) * 2;
-    o[0] = make_float4(b[0], b[1], b[9], b[10]);
-    o[1] = make_float4(b[81], b[82], b[90], b[91]);
-}
-cudaError_t launch_expand_bricks(const float* apron, float* stencil, uint32_t n_bricks, cudaStream_t s)
-{
-    for (uint32_t first = 0; first < n_bricks; first += 1u << 30) {
-        const uint32_t n = n_bricks - first < (1u << 30) ? n_bricks - first : (1u << 30);
-        vpt_expand_bricks_kernel<<<n, 512, 0, s>>>(apron, reinterpret_cast<float4*>(stencil), first);
-    }
-    return cudaGetLastError();
-}
-
 // ---------------------------------------------------------------- launchers
 cudaError_t upload_cie_table(const float* cie471x3) { return cudaMemcpyToSymbol(c_cie, cie471x3, sizeof(float) * 471 * 3); }
 

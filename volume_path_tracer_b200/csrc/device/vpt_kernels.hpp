@@ -33,7 +33,6 @@ cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool 
 int render_blocks_per_sm(int variant, bool trace, bool count);
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
 cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);
-cudaError_t launch_expand_bricks(const float* apron, float* stencil, uint32_t n_bricks, cudaStream_t s);
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);
 
 } // namespace vptd

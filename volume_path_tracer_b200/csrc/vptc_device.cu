@@ -42,7 +42,6 @@ struct vptc_ctx {
     CountersDev* counters = nullptr;
     bool count = false;
     int variant = 2; // render kernel variant (vptc_set_kernel_variant)
-    bool stencil_bricks = true; // expand bricks to the 8-corner stencil layout at set_volume (VPT_STENCIL_BRICKS=0: keep apron bricks)
     int sched_thresh[4] = {12, 8, 8, 12};
     float last_ms = 0.0f;
     vptc_counters last_counters{};
@@ -82,21 +81,6 @@ int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
     CU(up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4));
     CU(up(&g.bricks, b.bricks.data(), b.bricks.size() * 4));
     CU(cudaStreamSynchronize(ctx->stream));
-    // Expand to stencil bricks (8 corners per base voxel, one 32-byte sector per trilinear fetch) when HBM allows.
-    g.dev.stencil_bricks = 0;
-    const size_t stencil_bytes = size_t(b.header.n_bricks) * STENCIL_STRIDE * sizeof(float);
-    size_t free_b = 0, total_b = 0;
-    CU(cudaMemGetInfo(&free_b, &total_b));
-    if (ctx->stencil_bricks && b.header.n_bricks > 0 && stencil_bytes < free_b / 2) {
-        void* st = nullptr;
-        CU(cudaMalloc(&st, stencil_bytes));
-        CU(launch_expand_bricks(static_cast<const float*>(g.bricks), static_cast<float*>(st), b.header.n_bricks, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
-        cudaFree(g.bricks);
-        g.bytes += stencil_bytes - b.bricks.size() * 4;
-        g.bricks = st;
-        g.dev.stencil_bricks = 1;
-    }
     g.dev.cells = static_cast<const uint32_t*>(g.cells);
     g.dev.slots = static_cast<const Slot*>(g.slots);
     g.dev.tile_value = static_cast<const float*>(g.tile_value);
@@ -178,7 +162,6 @@ int vptc_create(vptc_ctx** out, int device)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
     CU(upload_cie_table(vpt_host::cie_table()));
     if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(2, std::max(0, std::atoi(v)));
-    if (const char* v = std::getenv("VPT_STENCIL_BRICKS")) ctx->stencil_bricks = std::atoi(v) != 0;
     if (const char* v = std::getenv("VPT_SCHED_THRESH")) // "setup,dda,sample,eval" lanes (tuning aid)
         std::sscanf(v, "%d,%d,%d,%d", &ctx->sched_thresh[0], &ctx->sched_thresh[1], &ctx->sched_thresh[2], &ctx->sched_thresh[3]);
     *out = c.release();
