@@ -47,20 +47,33 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="dense512", help="fire | fire_lowscattering | wdas_cloud | dense512 | wdas_cloud_4k")
-    ap.add_argument("--waves-per-step", type=int, default=32)
+    ap.add_argument("--waves-per-step", type=int, default=128)
     ap.add_argument("--volume-scale", type=float, default=1.0, help="resolution factor of the synthetic volume (1 = the named shape)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
 
 
-def load_workload(args):
+def load_workload(args, rank=0, world=1, barrier=None):
+    """Synthesise the named procedural volume. With several ranks, rank 0 synthesises once and the others read the
+    `.nvdb` it wrote (the product's own writer/reader), instead of every rank burning the host cores on the same work."""
     from volume_path_tracer_b200 import api, scenes
     scene, spec = scenes.load_config(args.config)
     if args.volume_scale != 1.0:
         spec = spec.scaled(args.volume_scale)
     t = time.time()
-    grids = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
+    if world == 1:
+        grids = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
+    else:
+        shm = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
+        path = shm / f"vpt_bench_{os.environ.get('MASTER_PORT', '0')}_{args.config}_{args.volume_scale}.nvdb"
+        if rank == 0:
+            api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor).write(path)
+        barrier()
+        grids = api.VolumeGrids.read_from_file(path)
+        barrier()
+        if rank == 0:
+            path.unlink(missing_ok=True)
     return scene, spec, grids, time.time() - t
 
 
@@ -219,7 +232,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    scene, spec, grids, synth_s = load_workload(args)
+    def host_barrier():
+        if world > 1:
+            dist.barrier()
+    scene, spec, grids, synth_s = load_workload(args, rank, world, host_barrier)
     K, Wu, M = args.steps, args.warmup, args.waves_per_step
     W, H = scene.width, scene.height
     px_step = W * H * M

@@ -7,6 +7,8 @@ from volume_path_tracer_b200 import api, scenes
 variants = [int(v) for v in os.environ.get("VARIANTS", "1,2").split(",")]
 threshes = os.environ.get("THRESH", "").split(";") if os.environ.get("THRESH") else [None]  # "12,8,8,12;16,8,8,16"
 cases = [("fire", 1.0, 16), ("fire_lowscattering", 1.0, 16), ("wdas_cloud", 0.25, 8), ("dense512", 1.0, 8)]
+if os.environ.get("WAVES"):  # override the waves per launch of every case
+    cases = [(n, f, int(os.environ["WAVES"])) for n, f, _ in cases]
 if os.environ.get("CASES"):
     cases = [c for c in cases if c[0] in os.environ["CASES"].split(",")]
 for name, factor, waves in cases:

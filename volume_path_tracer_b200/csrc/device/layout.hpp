@@ -70,6 +70,8 @@ struct SceneDev {
 
 struct CountersDev {
     unsigned long long pixel_samples, density_evals, temperature_evals, majorant_fetches, rng_draws, scatter_events, shadow_rays;
+    // warp-scheduling diagnostics of the sched kernel (COUNT builds): iterations, and per stage {times run, lanes served}
+    unsigned long long sched_iters, sched_runs[3], sched_lanes[3], sched_waiting, sched_exited;
 };
 
 } // namespace vptd

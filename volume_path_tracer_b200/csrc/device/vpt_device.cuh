@@ -14,6 +14,14 @@
 #include "layout.hpp"
 #include "libm_exact.cuh"
 
+// Rarely-taken helpers (general trilinear fetch, blackbody lookup): inlined by default; -DVPT_COLD_NOINLINE keeps them
+// out of line (an A/B switch for instruction-cache experiments).
+#ifdef VPT_COLD_NOINLINE
+#define VPT_COLD_INLINE __noinline__
+#else
+#define VPT_COLD_INLINE __forceinline__
+#endif
+
 namespace vptd {
 
 struct V3 { float x, y, z; };

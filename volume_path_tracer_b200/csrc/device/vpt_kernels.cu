@@ -36,7 +36,7 @@ __device__ __noinline__ V3 spectrum_to_xyz_direct(float T) // T >= 49900 K: dire
     const float Y = 106.856895f;
     return mk(acc[0] / Y, acc[1] / Y, acc[2] / Y);
 }
-__device__ __forceinline__ V3 blackbody_xyz(const float* __restrict__ bb, float T)
+__device__ VPT_COLD_INLINE V3 blackbody_xyz(const float* __restrict__ bb, float T)
 {
     if (!isfinite(T)) { const float n = __int_as_float(0x7fc00000); return mk(n, n, n); }
     if (T <= 0.0f) return mk(0.0f, 0.0f, 0.0f);

@@ -24,7 +24,7 @@ struct RenderArgs {
     float* trace_xyz;
     uint32_t* trace_ndraws;
     CountersDev* counters;        // COUNT builds
-    int sched_thresh[4];          // variant 2: lanes needed to run SETUP / DDA / SAMPLE / EVAL in an iteration
+    int sched_thresh[4];          // variant 2: lanes needed to run SETUP / HOT / - / EVAL in an iteration
 };
 
 cudaError_t upload_cie_table(const float* cie471x3);

@@ -49,6 +49,19 @@ __device__ __forceinline__ float majorant_cached(const GridDev& G, CellCache& cc
     if (c & CELL_KIND_TILE) return __ldg(&G.tile_majorant[c & CELL_INDEX_MASK]);
     return load_slot(G, slot_index(c, x, y, z)).majorant;
 }
+// Base voxel in a tile / background (its corners may still reach into leaves): 8 full getValue descents. Rare, and
+// deliberately NOT inlined — the render loop has to stay small for the instruction cache.
+__device__ VPT_COLD_INLINE float trilinear_general(const GridDev& G, int x, int y, int z, float u, float v, float w)
+{
+    const float v000 = value_at(G, x, y, z),         v001 = value_at(G, x, y, z + 1);
+    const float v010 = value_at(G, x, y + 1, z),     v011 = value_at(G, x, y + 1, z + 1);
+    const float v100 = value_at(G, x + 1, y, z),     v101 = value_at(G, x + 1, y, z + 1);
+    const float v110 = value_at(G, x + 1, y + 1, z), v111 = value_at(G, x + 1, y + 1, z + 1);
+    const float a00 = v000 + w * (v001 - v000), a01 = v010 + w * (v011 - v010);
+    const float a10 = v100 + w * (v101 - v100), a11 = v110 + w * (v111 - v110);
+    const float b0 = a00 + v * (a01 - a00), b1 = a10 + v * (a11 - a10);
+    return b0 + u * (b1 - b0);
+}
 // trilinear() of vpt_device.cuh with the cached cell code for the base voxel.
 __device__ __forceinline__ float trilinear_cached(const GridDev& G, CellCache& cc, float px, float py, float pz)
 {
@@ -69,12 +82,7 @@ __device__ __forceinline__ float trilinear_cached(const GridDev& G, CellCache& c
             fast = true;
         }
     }
-    if (!fast) {
-        v000 = value_at(G, x, y, z);         v001 = value_at(G, x, y, z + 1);
-        v010 = value_at(G, x, y + 1, z);     v011 = value_at(G, x, y + 1, z + 1);
-        v100 = value_at(G, x + 1, y, z);     v101 = value_at(G, x + 1, y, z + 1);
-        v110 = value_at(G, x + 1, y + 1, z); v111 = value_at(G, x + 1, y + 1, z + 1);
-    }
+    if (!fast) return trilinear_general(G, x, y, z, u, v, w);
     const float a00 = v000 + w * (v001 - v000), a01 = v010 + w * (v011 - v010);
     const float a10 = v100 + w * (v101 - v100), a11 = v110 + w * (v111 - v110);
     const float b0 = a00 + v * (a01 - a00), b1 = a10 + v * (a11 - a10);

@@ -19,6 +19,17 @@ namespace vptd {
 #define VPT_SCHED_MIN_BLOCKS 5 // resident 128-thread blocks per SM the register allocation must allow
 #endif
 
+// Explicit reconvergence points (A/B switches). The kernel's speed hangs on where ptxas lets the lanes of a stage
+// rejoin: an edit as small as one conditional load in the job fetch made SETUP's ray begin run at 4.5 instead of 7.7
+// lanes and the kernel 25 % slower (profiles/r01_codegen_cliff.txt). -DVPT_SYNC_SETUP=1 pins the rejoin with a
+// __syncwarp over the lanes that entered the stage; it costs ~1 % when the compiler already does the right thing
+// (the present code), so it is off — turn it on first when an edit to SETUP slows the kernel unexpectedly.
+#ifndef VPT_SYNC_SETUP
+#define VPT_SYNC_SETUP 0
+#endif
+#ifndef VPT_SYNC_HOT
+#define VPT_SYNC_HOT 0 // same for HOT's two halves; measured -8 %, kept for experiments only
+#endif
 enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
 
 template <bool TRACE, bool COUNT>
@@ -37,7 +48,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     const unsigned FULL = 0xffffffffu;
     const int th_setup = max(1, A.sched_thresh[0]), th_hot = max(1, A.sched_thresh[1]), th_eval = max(1, A.sched_thresh[3]);
     Stats st = {0, 0, 0, 0, 0, 0};
-    unsigned long long draws_total = 0;
+    unsigned long long draws_total = 0, sd_iters = 0, sd_runs[3] = {0, 0, 0}, sd_lanes[3] = {0, 0, 0}, sd_wait = 0, sd_exit = 0;
     Rng rng; rng.state = 0; rng.draws = 0;
     CellCache cc, ct;
     cc.reset(); ct.reset();
@@ -67,8 +78,18 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         const bool run_setup = n_setup >= th_setup || n_setup == n_max;
         const bool run_hot = n_hot >= th_hot || n_hot == n_max;
         const bool run_eval = n_eval >= th_eval || n_eval == n_max;
+        if (COUNT && (threadIdx.x & 31) == 0) {
+            ++sd_iters;
+            sd_runs[0] += run_setup && n_setup > 0; sd_runs[1] += run_hot && n_hot > 0; sd_runs[2] += run_eval && n_eval > 0;
+            sd_lanes[0] += run_setup ? n_setup : 0; sd_lanes[1] += run_hot ? n_hot : 0; sd_lanes[2] += run_eval ? n_eval : 0;
+            sd_wait += (run_setup ? 0 : n_setup) + (run_hot ? 0 : n_hot) + (run_eval ? 0 : n_eval);
+            sd_exit += 32 - n_setup - n_hot - n_eval;
+        }
 
         // ------------------------------------------------------------ SETUP: pixel / job bookkeeping, ray begin
+#if VPT_SYNC_SETUP
+        const unsigned setup_mask = __ballot_sync(FULL, run_setup && stage == ST_SETUP);
+#endif
         if (run_setup && stage == ST_SETUP) {
             if (sub == PH_NEXT_PIXEL) {
                 if (pixel_open) { // film(y,x) += (imaging_ratio * L, 1)   worker.cpp:203-204
@@ -127,6 +148,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 shadow = false;
                 depth += 2; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
             }
+#if VPT_SYNC_SETUP
+            __syncwarp(setup_mask); // the three sub-phases rejoin here: ray begin runs with every SETUP lane
+#endif
             if (stage != ST_EXIT) {
                 if (!shadow && depth >= S.max_depth) { // bounce loop out of depth: not terminated -> infinite light (:198-200)
                     L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2];
@@ -144,6 +168,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
 
         // ------------------------------------------------------------ HOT: one HDDA step and/or one free-flight draw
+#if VPT_SYNC_HOT
+        const unsigned hot_mask = __ballot_sync(FULL, run_hot && stage == ST_HOT);
+#endif
         if (run_hot && stage == ST_HOT) {
             if (!m.has_seg) { // RayMajorantIterator::next, one step   volume.cpp:53-71
                 bool closed;
@@ -162,6 +189,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
                 }
             }
+#if VPT_SYNC_HOT
+            __syncwarp(hot_mask);
+#endif
             if (m.has_seg && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
                 pend_u = rng.uniform();
                 // ~85 % of the draws overshoot the segment. Only the DECISION `t < seg.t1` matters then, not t itself, so
@@ -244,6 +274,12 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         atomicAdd(&A.counters->rng_draws, draws_total);
         atomicAdd(&A.counters->scatter_events, (unsigned long long)st.scatter_events);
         atomicAdd(&A.counters->shadow_rays, (unsigned long long)st.shadow_rays);
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&A.counters->sched_iters, sd_iters);
+            for (int i = 0; i < 3; ++i) { atomicAdd(&A.counters->sched_runs[i], sd_runs[i]); atomicAdd(&A.counters->sched_lanes[i], sd_lanes[i]); }
+            atomicAdd(&A.counters->sched_waiting, sd_wait);
+            atomicAdd(&A.counters->sched_exited, sd_exit);
+        }
     }
 }
 

@@ -124,6 +124,13 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
         CountersDev h;
         CU(cudaMemcpy(&h, ctx->counters, sizeof(h), cudaMemcpyDeviceToHost));
         ctx->last_counters = {h.pixel_samples, h.density_evals, h.temperature_evals, h.majorant_fetches, h.rng_draws, h.scatter_events, h.shadow_rays};
+        if (std::getenv("VPT_SCHED_STATS") && h.sched_iters) { // development aid: where the lanes of a warp spend their iterations
+            const double it = double(h.sched_iters);
+            std::fprintf(stderr, "[sched] warp-iterations %.4g; per iteration: SETUP run %.3f (%.1f lanes when run), HOT run %.3f (%.1f), EVAL run %.3f (%.1f); waiting %.2f lanes, exited %.2f lanes\n",
+                         it, h.sched_runs[0] / it, double(h.sched_lanes[0]) / double(h.sched_runs[0] ? h.sched_runs[0] : 1), h.sched_runs[1] / it,
+                         double(h.sched_lanes[1]) / double(h.sched_runs[1] ? h.sched_runs[1] : 1), h.sched_runs[2] / it,
+                         double(h.sched_lanes[2]) / double(h.sched_runs[2] ? h.sched_runs[2] : 1), h.sched_waiting / it, h.sched_exited / it);
+        }
     }
     return VPTC_OK;
 }
