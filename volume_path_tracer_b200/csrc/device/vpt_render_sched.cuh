@@ -16,7 +16,7 @@
 namespace vptd {
 
 #ifndef VPT_SCHED_MIN_BLOCKS
-#define VPT_SCHED_MIN_BLOCKS 5 // resident 128-thread blocks per SM the register allocation must allow
+#define VPT_SCHED_MIN_BLOCKS 7 // resident 128-thread blocks per SM the register allocation must allow (72 registers)
 #endif
 
 // Explicit reconvergence points (A/B switches). The kernel's speed hangs on where ptxas lets the lanes of a stage
@@ -46,27 +46,38 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     const SceneDev& S = A.scene;
     const GridDev& G = A.density;
     const unsigned FULL = 0xffffffffu;
-    const int th_setup = max(1, A.sched_thresh[0]), th_hot = max(1, A.sched_thresh[1]), th_eval = max(1, A.sched_thresh[3]);
     Stats st = {0, 0, 0, 0, 0, 0};
     unsigned long long draws_total = 0, sd_iters = 0, sd_runs[3] = {0, 0, 0}, sd_lanes[3] = {0, 0, 0}, sd_wait = 0, sd_exit = 0;
     Rng rng; rng.state = 0; rng.draws = 0;
-    CellCache cc, ct;
-    cc.reset(); ct.reset();
+    CellCache cc;
+    cc.reset();
     March m;
     m.has_seg = false;
-    V3 pos = mk(0, 0, 0), rd = mk(0, 0, 1), L = mk(0, 0, 0), pos_idx = mk(0, 0, 0);
-    float T_ray = 1.0f, pend_u = 0.0f;
-    unsigned int depth = 0;
+    float pend_u = 0.0f;
     bool shadow = false, pixel_open = false;
     int stage = ST_SETUP, sub = PH_NEXT_PIXEL;
     unsigned long long j = 0;
-    int x0 = 0, y0 = 0, sx = 0, sy = 0, x = 0, y = 0;
+    // COLD per-lane state lives in shared memory, one word column per lane (conflict-free): everything HOT never
+    // touches — path origin/direction/radiance, shadow transmittance, depth, the job's pixel bookkeeping, the
+    // temperature grid's cell cache. That is 21 registers the hot loop does not have to carry, which is what lets
+    // the kernel fit VPT_SCHED_MIN_BLOCKS resident blocks per SM without spilling.
+    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_WORDS = 21 };
+    __shared__ uint32_t cold[C_WORDS][VPT_BLOCK_THREADS];
+    const int lane_col = threadIdx.x;
+#define CLDF(i) __uint_as_float(cold[i][lane_col])
+#define CLDI(i) int(cold[i][lane_col])
+#define CSTF(i, v) (cold[i][lane_col] = __float_as_uint(v))
+#define CSTI(i, v) (cold[i][lane_col] = uint32_t(v))
+#define CLD3(i) mk(CLDF(i), CLDF((i) + 1), CLDF((i) + 2))
+#define CST3(i, v) do { CSTF(i, (v).x); CSTF((i) + 1, (v).y); CSTF((i) + 2, (v).z); } while (0)
+    for (int i = 0; i < C_WORDS; ++i) cold[i][lane_col] = 0u; // sx = sy = x = y = 0: the first SETUP fetches a job
+    CSTI(C_CT, INT_MIN); CSTI(C_CT + 1, INT_MIN); CSTI(C_CT + 2, INT_MIN); // CellCache::reset()
 
     // the ray left the volume (iterator.next() -> nullopt): back to SETUP
 #define VPT_RAY_FINISHED()                                                                            \
     do {                                                                                              \
         if (shadow) sub = PH_AFTER_SHADOW;                                                            \
-        else { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; sub = PH_NEXT_PIXEL; } \
+        else { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; } \
         stage = ST_SETUP;                                                                             \
     } while (0)
 
@@ -75,9 +86,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         const int n_eval = __popc(__ballot_sync(FULL, stage == ST_EVAL));
         const int n_max = max(n_setup, max(n_hot, n_eval));
         if (n_max == 0) break; // every lane has exited
-        const bool run_setup = n_setup >= th_setup || n_setup == n_max;
-        const bool run_hot = n_hot >= th_hot || n_hot == n_max;
-        const bool run_eval = n_eval >= th_eval || n_eval == n_max;
+        const bool run_setup = n_setup >= A.sched_thresh[0] || n_setup == n_max;
+        const bool run_hot = n_hot >= A.sched_thresh[1] || n_hot == n_max;
+        const bool run_eval = n_eval >= A.sched_thresh[3] || n_eval == n_max;
         if (COUNT && (threadIdx.x & 31) == 0) {
             ++sd_iters;
             sd_runs[0] += run_setup && n_setup > 0; sd_runs[1] += run_hot && n_hot > 0; sd_runs[2] += run_eval && n_eval > 0;
@@ -91,8 +102,12 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         const unsigned setup_mask = __ballot_sync(FULL, run_setup && stage == ST_SETUP);
 #endif
         if (run_setup && stage == ST_SETUP) {
+            V3 rd = mk(0.0f, 0.0f, 1.0f); // direction of the ray to begin (unused by a shadow ray: shadow_dir)
+            unsigned int depth = 0;
             if (sub == PH_NEXT_PIXEL) {
+                int x0 = CLDI(C_X0), y0 = CLDI(C_Y0), sx = CLDI(C_SX), sy = CLDI(C_SY), x = CLDI(C_X), y = CLDI(C_Y);
                 if (pixel_open) { // film(y,x) += (imaging_ratio * L, 1)   worker.cpp:203-204
+                    const V3 L = CLD3(C_L);
                     if (COUNT) ++st.pixel_samples;
                     if (TRACE) {
                         const size_t slot = size_t(j) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
@@ -119,12 +134,14 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         const int64_t tx0 = int64_t(tile % uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tile / uint64_t(S.ntx)) * S.th;
                         x0 = int(tx0); y0 = int(ty0);
                         sx = int(min(S.W - tx0, S.tw)); sy = int(min(S.H - ty0, S.th));
+                        CSTI(C_X0, x0); CSTI(C_Y0, y0); CSTI(C_SX, sx); CSTI(C_SY, sy);
                         rng.begin_job(S.seed, jid);
                         x = 0; y = 0;
                     }
                     if (S.single_pixel_enabled && (int64_t(x0 + x) != S.single_pixel_x || int64_t(y0 + y) != S.single_pixel_y)) continue;
                     break;
                 }
+                CSTI(C_X, x); CSTI(C_Y, y);
                 if (stage != ST_EXIT) { // camera path start   worker.cpp:121-128, camera.hpp:14-23
                     const float j0 = rng.uniform(), j1 = rng.uniform();
                     const float jm = S.use_jitter ? 0.5f : 0.0f;
@@ -132,37 +149,42 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     rd = normalized(mk(sum3(S.cam_m[0] * rx, S.cam_m[1] * ry, S.cam_m[2] * 0.0f) + S.cam_t[0],
                                        sum3(S.cam_m[3] * rx, S.cam_m[4] * ry, S.cam_m[5] * 0.0f) + S.cam_t[1],
                                        sum3(S.cam_m[6] * rx, S.cam_m[7] * ry, S.cam_m[8] * 0.0f) + S.cam_t[2]));
-                    pos = mk(S.cam_pos[0], S.cam_pos[1], S.cam_pos[2]);
-                    L = mk(0.0f, 0.0f, 0.0f);
-                    depth = 0; shadow = false; pixel_open = true;
+                    CST3(C_RD, rd);
+                    CSTF(C_POS, S.cam_pos[0]); CSTF(C_POS + 1, S.cam_pos[1]); CSTF(C_POS + 2, S.cam_pos[2]);
+                    CSTF(C_L, 0.0f); CSTF(C_L + 1, 0.0f); CSTF(C_L + 2, 0.0f);
+                    CSTI(C_DEPTH, 0);
+                    shadow = false; pixel_open = true;
                 }
             } else if (sub == PH_BEGIN_SHADOW) { // sample_Ld   worker.cpp:59-66
-                shadow = true; T_ray = 1.0f;
+                shadow = true; CSTF(C_TRAY, 1.0f);
                 if (COUNT) ++st.shadow_rays;
             } else { // PH_AFTER_SHADOW: worker.cpp:88-89 then :175-183
                 const V3 wi = mk(S.dist_wi[0], S.dist_wi[1], S.dist_wi[2]);
-                const float k = henyey_greenstein(dot3(rd, wi), S.g) * T_ray;
-                L.x += k * S.dist_Li[0]; L.y += k * S.dist_Li[1]; L.z += k * S.dist_Li[2];
+                rd = CLD3(C_RD);
+                const float k = henyey_greenstein(dot3(rd, wi), S.g) * CLDF(C_TRAY);
+                CSTF(C_L, CLDF(C_L) + k * S.dist_Li[0]); CSTF(C_L + 1, CLDF(C_L + 1) + k * S.dist_Li[1]); CSTF(C_L + 2, CLDF(C_L + 2) + k * S.dist_Li[2]);
                 const float u0 = rng.uniform(), u1 = rng.uniform();
                 rd = sample_henyey_greenstein(rd, u0, u1, S.g);
+                CST3(C_RD, rd);
                 shadow = false;
-                depth += 2; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
+                depth = unsigned(CLDI(C_DEPTH)) + 2u; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
+                CSTI(C_DEPTH, depth);
             }
 #if VPT_SYNC_SETUP
             __syncwarp(setup_mask); // the three sub-phases rejoin here: ray begin runs with every SETUP lane
 #endif
             if (stage != ST_EXIT) {
                 if (!shadow && depth >= S.max_depth) { // bounce loop out of depth: not terminated -> infinite light (:198-200)
-                    L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2];
+                    CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]);
                     sub = PH_NEXT_PIXEL;
                 } else {
                     bool ray_done;
                     const RayDir rdir = shadow ? shadow_dir : make_ray_dir(G, rd);
-                    if (flat_begin_ray_dir<COUNT>(m, G, cc, pos, rdir, ray_done, st)) {
+                    if (flat_begin_ray_dir<COUNT>(m, G, cc, CLD3(C_POS), rdir, ray_done, st)) {
                         if (ray_done) VPT_RAY_FINISHED();
                         else stage = ST_HOT;
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
-                    else { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; sub = PH_NEXT_PIXEL; }
+                    else { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; }
                 }
             }
         }
@@ -214,6 +236,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
             const float t = m.seg_t0 + dt_m / m.scale;
             stage = ST_HOT;
             float density = 0.0f;
+            V3 pos_idx = mk(0.0f, 0.0f, 0.0f);
             if (t < m.seg_t1) {
                 m.seg_t0 = t;
                 const V3 p = m.at(t);
@@ -228,12 +251,13 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
             if (density > 0.0f) {
                 if (shadow) { // ratio tracking + Russian roulette
                     const float sigma_n = fmaxf(0.0f, sigma_maj - S.sigma_t * density);
-                    T_ray *= sigma_n / sigma_maj;
+                    float T_ray = CLDF(C_TRAY) * (sigma_n / sigma_maj);
                     if (T_ray <= 0.05f) {
                         if (rng.uniform() < 0.75f) T_ray = 0.0f;
                         else T_ray /= 0.25f;
                     }
                     if (T_ray <= 0.0f) { T_ray = 0.0f; sub = PH_AFTER_SHADOW; stage = ST_SETUP; }
+                    CSTF(C_TRAY, T_ray);
                 } else {
                     const V3 point = index_to_world(G, pos_idx);
                     const float p_a = (S.sigma_a * density) / sigma_maj;
@@ -242,11 +266,14 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     if (S.has_temperature) {
                         const V3 tc = world_to_index(A.temperature, point);
                         if (COUNT) ++st.temperature_evals;
+                        CellCache ct;
+                        ct.cx = CLDI(C_CT); ct.cy = CLDI(C_CT + 1); ct.cz = CLDI(C_CT + 2); ct.code = cold[C_CT + 3][lane_col];
                         const float temp_adim = trilinear_cached(A.temperature, ct, tc.x, tc.y, tc.z);
+                        CSTI(C_CT, ct.cx); CSTI(C_CT + 1, ct.cy); CSTI(C_CT + 2, ct.cz); cold[C_CT + 3][lane_col] = ct.code;
                         const float temp_K = temp_adim * S.temperature_scale + S.temperature_offset;
                         const V3 e = blackbody_xyz(bb, temp_K);
                         const float k = p_a * S.le_scale;
-                        L.x += k * e.x; L.y += k * e.y; L.z += k * e.z;
+                        CSTF(C_L, CLDF(C_L) + k * e.x); CSTF(C_L + 1, CLDF(C_L + 1) + k * e.y); CSTF(C_L + 2, CLDF(C_L + 2) + k * e.z);
                     }
                     float u = rng.uniform() * (((0.0f + p_n) + p_a) + p_s); // sample_discrete  random.hpp:31-47
                     u -= p_n;
@@ -256,9 +283,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         if (u <= 0.0f) sub = PH_NEXT_PIXEL; // absorption: terminated, no infinite light
                         else {                               // scatter (also the fallback choice)
                             if (COUNT) ++st.scatter_events;
-                            pos = point;
+                            CST3(C_POS, point);
                             if (S.dist_light_on) sub = PH_BEGIN_SHADOW;
-                            else { T_ray = 0.0f; sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
+                            else { CSTF(C_TRAY, 0.0f); sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
                         }
                     }
                 }
@@ -266,6 +293,12 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
     }
 #undef VPT_RAY_FINISHED
+#undef CLDF
+#undef CLDI
+#undef CSTF
+#undef CSTI
+#undef CLD3
+#undef CST3
     if (COUNT) {
         atomicAdd(&A.counters->pixel_samples, (unsigned long long)st.pixel_samples);
         atomicAdd(&A.counters->density_evals, (unsigned long long)st.density_evals);

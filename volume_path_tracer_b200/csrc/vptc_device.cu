@@ -107,7 +107,7 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     A.bb_table = ctx->bb_table;
     A.queue = ctx->queue;
     A.counters = ctx->counters;
-    for (int i = 0; i < 4; ++i) A.sched_thresh[i] = ctx->sched_thresh[i];
+    for (int i = 0; i < 4; ++i) A.sched_thresh[i] = std::max(1, ctx->sched_thresh[i]); // the kernel relies on >= 1
     CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
     const int per_sm = render_blocks_per_sm(ctx->variant, trace, ctx->count);
