@@ -42,7 +42,9 @@ for r in rows[2:]:
 
     def num(k):
         if k not in col:
-            k = [h for h in col if h.endswith(k)][0]
+            hits = [h for h in col if h.endswith(k)]
+            if not hits: return float('nan')  # section-limited capture: metric absent
+            k = hits[0]
         v, u = r[col[k]].replace(",", ""), units[col[k]]
         return float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(u, 1.0)
     if dur:

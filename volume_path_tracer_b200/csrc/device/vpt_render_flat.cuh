@@ -22,20 +22,21 @@ namespace vptd {
 // the same cell (a dense 512^3 grid has only 4^3 of them), which removes two of the three dependent loads of an
 // HDDA step (getDim probe + majorant descent) and one of the two of a trilinear fetch.
 struct CellCache {
-    int cx, cy, cz;
-    uint32_t code;
-    __device__ __forceinline__ void reset() { cx = cy = cz = INT_MIN; code = 0u; }
+    int x, y, z;   // any voxel of the cached cell. Cells are 128-aligned in index space (cell_org is a multiple of 4096,
+    uint32_t code; // bake.cpp), so "same cell" is "all bits above the low 7 equal": one xor/or chain instead of 3 sub+shift+compare
+    // The sentinel voxel INT_MIN lies outside every grid bake.cpp accepts (|coordinate| <= 2^30): background, dim 4096.
+    __device__ __forceinline__ void reset() { x = y = z = INT_MIN; code = CELL_KIND_TILE | (2u << CELL_DIM_SHIFT); }
 };
 __device__ __forceinline__ uint32_t cell_code_cached(const GridDev& G, CellCache& cc, int x, int y, int z)
 {
+    if (unsigned((x ^ cc.x) | (y ^ cc.y) | (z ^ cc.z)) < 128u) return cc.code;
     const int cx = (x - G.cell_org[0]) >> 7, cy = (y - G.cell_org[1]) >> 7, cz = (z - G.cell_org[2]) >> 7;
-    if (cx == cc.cx && cy == cc.cy && cz == cc.cz) return cc.code;
     uint32_t code;
     if (unsigned(cx) >= unsigned(G.cell_dim[0]) || unsigned(cy) >= unsigned(G.cell_dim[1]) || unsigned(cz) >= unsigned(G.cell_dim[2]))
         code = CELL_KIND_TILE | (2u << CELL_DIM_SHIFT);
     else
         code = __ldg(&G.cells[(cx * G.cell_dim[1] + cy) * G.cell_dim[2] + cz]); // < 2^27 cells (bake.cpp): 32-bit index
-    cc.cx = cx; cc.cy = cy; cc.cz = cz; cc.code = code;
+    cc.x = x; cc.y = y; cc.z = z; cc.code = code;
     return code;
 }
 __device__ __forceinline__ int dim_of_code(uint32_t c)

@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
 #define CLD3(i) mk(CLDF(i), CLDF((i) + 1), CLDF((i) + 2))
 #define CST3(i, v) do { CSTF(i, (v).x); CSTF((i) + 1, (v).y); CSTF((i) + 2, (v).z); } while (0)
     for (int i = 0; i < C_WORDS; ++i) cold[i][lane_col] = 0u; // sx = sy = x = y = 0: the first SETUP fetches a job
-    CSTI(C_CT, INT_MIN); CSTI(C_CT + 1, INT_MIN); CSTI(C_CT + 2, INT_MIN); // CellCache::reset()
+    { CellCache r; r.reset(); CSTI(C_CT, r.x); CSTI(C_CT + 1, r.y); CSTI(C_CT + 2, r.z); cold[C_CT + 3][lane_col] = r.code; }
 
     // the ray left the volume (iterator.next() -> nullopt): back to SETUP
 #define VPT_RAY_FINISHED()                                                                            \
@@ -267,9 +267,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         const V3 tc = world_to_index(A.temperature, point);
                         if (COUNT) ++st.temperature_evals;
                         CellCache ct;
-                        ct.cx = CLDI(C_CT); ct.cy = CLDI(C_CT + 1); ct.cz = CLDI(C_CT + 2); ct.code = cold[C_CT + 3][lane_col];
+                        ct.x = CLDI(C_CT); ct.y = CLDI(C_CT + 1); ct.z = CLDI(C_CT + 2); ct.code = cold[C_CT + 3][lane_col];
                         const float temp_adim = trilinear_cached(A.temperature, ct, tc.x, tc.y, tc.z);
-                        CSTI(C_CT, ct.cx); CSTI(C_CT + 1, ct.cy); CSTI(C_CT + 2, ct.cz); cold[C_CT + 3][lane_col] = ct.code;
+                        CSTI(C_CT, ct.x); CSTI(C_CT + 1, ct.y); CSTI(C_CT + 2, ct.z); cold[C_CT + 3][lane_col] = ct.code;
                         const float temp_K = temp_adim * S.temperature_scale + S.temperature_offset;
                         const V3 e = blackbody_xyz(bb, temp_K);
                         const float k = p_a * S.le_scale;

@@ -88,6 +88,9 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
     std::memcpy(h.invMat, g->map.invMatF, sizeof(h.invMat));
     std::memcpy(h.vec, g->map.vecF, sizeof(h.vec));
     for (int a = 0; a < 3; ++a) { h.bbox_min[a] = tv.root->bbox[a]; h.bbox_max[a] = tv.root->bbox[3 + a]; }
+    for (int a = 0; a < 3; ++a) // keeps every device-side coordinate sum in int32 and the cell caches' INT_MIN sentinel outside the grid
+        if (h.bbox_min[a] <= h.bbox_max[a] && (h.bbox_min[a] < -(1 << 30) || h.bbox_max[a] > (1 << 30)))
+            throw std::runtime_error("bake: grid index bounding box exceeds +-2^30");
 
     // ---- tiles: index 0 = {background, inactive} ----
     out.tile_value.assign(1, tv.root->background);

@@ -42,7 +42,7 @@ struct vptc_ctx {
     CountersDev* counters = nullptr;
     bool count = false;
     int variant = 2; // render kernel variant (vptc_set_kernel_variant)
-    int sched_thresh[4] = {12, 8, 8, 12};
+    int sched_thresh[4] = {12, 8, 8, 16};
     float last_ms = 0.0f;
     vptc_counters last_counters{};
     int num_sms = 0;
