@@ -318,6 +318,22 @@ def run_ours(args):
         peak, peak_src = hbm_peak()
         k_ms = sum(kernel_ms) / len(kernel_ms)
         achieved = alg_bytes_per_sample * px_step / (k_ms * 1e-3) / 1e9
+        # DRAM traffic and issued warp instructions per pixel-sample come from the committed ncu --set full capture of this
+        # kernel on this workload (profiles/r01_ncu_constants.json); scaled to this launch's pixel-samples. None for other configs.
+        traffic = issue = None
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_constants.json")) as f:
+                ncu_c = json.load(f).get(args.config)
+            if ncu_c:
+                traffic = ncu_c["dram_bytes_per_pixel_sample"] * px_step
+                sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
+                peak_issue = torch.cuda.get_device_properties(local).multi_processor_count * 4 * sm_mhz * 1e6  # 4 schedulers/SM, 1 warp instr/clk each
+                ach_issue = ncu_c["warp_instructions_per_pixel_sample"] * px_step / (k_ms * 1e-3)
+                issue = {"bound": "warp-instruction issue (the binding limit of this kernel)", "achieved": ach_issue / 1e9, "peak": peak_issue / 1e9,
+                         "unit": "G warp-instr/s", "frac": ach_issue / peak_issue, "threads_per_warp_instruction": ncu_c["threads_per_warp_instruction"],
+                         "source": "warp instructions per pixel-sample from profiles/r01_ncu_constants.json x live kernel time"}
+        except (OSError, ValueError, KeyError):
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wu, "ms_per_step": total_ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -329,7 +345,7 @@ def run_ours(args):
                             "like the reference loads its grids once"},
             "gpu_launches": K,
             "kernel": "vpt_render_sched_kernel (variant 2; 1 launch per step per GPU)",
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": peak_src, "kernel_ms": k_ms,
                          "algorithmic_bytes_per_pixel_sample": alg_bytes_per_sample,
                          "per_pixel_sample": {"density_evals": cnt.density_evals / cnt.pixel_samples, "temperature_evals": cnt.temperature_evals / cnt.pixel_samples,
@@ -337,6 +353,8 @@ def run_ours(args):
                                               "scatter_events": cnt.scatter_events / cnt.pixel_samples}},
             "clocks": clk,
         }
+        if issue:
+            line["roofline"]["issue"] = issue
         if not args.no_cpu_baseline and world == 1:
             c = cpu_leg(scene, grids, 1, args.cpu_seconds)
             line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["threads"], "kind": "port", "sample": c["sample"], "note": c["kind_note"]}
