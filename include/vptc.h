@@ -173,6 +173,15 @@ VPTC_API int vptc_synth_volume(const char* kind, const int32_t dims[3], double v
 /* 8-bit RGB PNG (replaces Image<uchar,3>::save, src/image_io.cpp:18-58). */
 VPTC_API int vptc_write_png(const char* path, const uint8_t* rgb8, int64_t width, int64_t height);
 
+/* Progressive render checkpoint: the float4 film plus the next wave to render. The reference keeps both
+ * only in memory (film: src/main.cpp:58-60; the wave counter: TileProvider, src/tile_provider.cpp:27-38, stopped early by
+ * stop_at_next_wave :107-110 when the preview window closes); a headless multi-hour render needs them on disk.
+ * The file records a fingerprint of every scene field that determines the film (everything except num_waves and
+ * num_workers, so a resumed render may ask for more waves); vptc_film_load refuses a file whose size or fingerprint
+ * differs (VPTC_ERR_CONFIG) and returns VPTC_ERR_IO when the file is missing or truncated. Save is atomic (tmp + rename). */
+VPTC_API int vptc_film_save(const char* path, const vptc_scene* scene, const float* film_xyzw, uint32_t next_wave);
+VPTC_API int vptc_film_load(const char* path, const vptc_scene* scene, float* film_xyzw, uint32_t* next_wave);
+
 VPTC_API const char* vptc_version(void);
 
 #ifdef __cplusplus

@@ -2,6 +2,7 @@
 relative to the scene file, density-required / temperature-optional grids, [FATAL] + exit(1) on errors (main.cpp:26-56,
 volume_grids.cpp:36-67, logging.hpp:16) — and the image it writes equals film_to_image of the CPU oracle's film."""
 import json
+import os
 import subprocess
 
 import numpy as np
@@ -63,3 +64,67 @@ def test_cli_errors_are_fatal(api, scenes, tmp_path):
     scene_path = _scene(scenes, tmp_path, "../volumes/fire.nvdb")
     r = subprocess.run([str(VPT), str(scene_path), "o.png"], capture_output=True, text=True)
     assert r.returncode == 1 and 'does not contain the "density" grid' in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_progressive_save_and_resume(api, scenes, tmp_path):
+    """VPT_SAVE_EVERY rewrites the image while rendering; VPT_CHECKPOINT lets a second run with a larger
+    num_waves continue where the first stopped, and the result is the uninterrupted render bit for bit (one wave per
+    call: exactly one sample per pixel per call, so the film sums are order-independent)."""
+    from PIL import Image
+    grids = api.synth_volume("fire", (50, 60, 50), 1.0, 1, None)
+    (tmp_path / "volumes").mkdir()
+    grids.write(tmp_path / "volumes" / "fire.nvdb")
+    env = {**os.environ, "VPT_WAVES_PER_CALL": "1"}
+    full = tmp_path / "full.png"
+    p6 = _scene(scenes, tmp_path, "../volumes/fire.nvdb", waves=6)
+    r = subprocess.run([str(VPT), str(p6), str(full)], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr
+    # first leg: 4 waves, image rewritten every 2 waves, checkpoint kept
+    ck = tmp_path / "render.film"
+    out = tmp_path / "out.png"
+    p4 = _scene(scenes, tmp_path, "../volumes/fire.nvdb", waves=4)
+    r = subprocess.run([str(VPT), str(p4), str(out)], capture_output=True, text=True, timeout=300, env={**env, "VPT_SAVE_EVERY": "2", "VPT_CHECKPOINT": str(ck)})
+    assert r.returncode == 0, r.stderr
+    scene4, _ = api.read_configuration(p4)
+    film, nxt = api.film_load(ck, scene4)
+    assert nxt == 5 and (film[..., 3] == 4).all()
+    # second leg: the scene now asks for 6 waves; the run resumes at wave 5
+    p6 = _scene(scenes, tmp_path, "../volumes/fire.nvdb", waves=6)
+    r = subprocess.run([str(VPT), str(p6), str(out)], capture_output=True, text=True, timeout=300, env={**env, "VPT_CHECKPOINT": str(ck)})
+    assert r.returncode == 0, r.stderr
+    assert "Resuming from checkpoint" in r.stderr and "Starting wave 5/6" in r.stderr and "Starting wave 4/6" not in r.stderr
+    scene6, _ = api.read_configuration(p6)
+    film, nxt = api.film_load(ck, scene6)
+    assert nxt == 7 and (film[..., 3] == 6).all()
+    assert np.array_equal(np.asarray(Image.open(out)), np.asarray(Image.open(full)))
+    # a checkpoint of another scene is refused the reference's way
+    d = json.loads(p6.read_text()); d["seed"] += 1; p6.write_text(json.dumps(d))
+    r = subprocess.run([str(VPT), str(p6), str(out)], capture_output=True, text=True, timeout=300, env={**env, "VPT_CHECKPOINT": str(ck)})
+    assert r.returncode == 1 and "[FATAL]" in r.stderr and "different scene" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_sigint_stops_at_a_wave_boundary_and_saves(api, scenes, tmp_path):
+    """Closing the reference's window stops at the next wave and still saves the image (tile_provider.cpp:107-110,
+    main.cpp:133-143); headless, SIGINT does the same and leaves a checkpoint to resume from."""
+    import signal, time
+    grids = api.synth_volume("fire", (50, 60, 50), 1.0, 1, None)
+    (tmp_path / "volumes").mkdir()
+    grids.write(tmp_path / "volumes" / "fire.nvdb")
+    p = _scene(scenes, tmp_path, "../volumes/fire.nvdb", size=(320, 240), waves=100000)
+    ck = tmp_path / "render.film"
+    out = tmp_path / "out.png"
+    proc = subprocess.Popen([str(VPT), str(p), str(out)], stderr=subprocess.PIPE, text=True,
+                            env={**os.environ, "VPT_WAVES_PER_CALL": "4", "VPT_CHECKPOINT": str(ck)})
+    seen = ""
+    t0 = time.time()
+    while "Starting wave 9/" not in seen and time.time() - t0 < 120:  # a few calls in
+        seen += proc.stderr.readline()
+    proc.send_signal(signal.SIGINT)
+    rest = proc.communicate(timeout=120)[1]
+    assert proc.returncode == 0, seen + rest
+    assert "Stopped at wave" in rest and out.exists()
+    scene, _ = api.read_configuration(p)
+    film, nxt = api.film_load(ck, scene)
+    assert nxt > 9 and (nxt - 1) % 4 == 0 and (film[..., 3] == nxt - 1).all()

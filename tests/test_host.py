@@ -269,3 +269,37 @@ def test_ragged_tiles_cover_image_once(oracle, api, scenes):
     # waves are additive: [1..3] == [1..2] + [3]
     a = np.zeros_like(film); vol.render(scene, a, first_wave=1, n_waves=2); vol.render(scene, a, first_wave=3, n_waves=1)
     assert np.array_equal(a, film)
+
+
+# ---------------------------------------------------------------- film checkpoint (film: main.cpp:58-60, wave counter: tile_provider.cpp:27-38)
+def test_film_checkpoint_roundtrip_and_refusals(api, scenes, tmp_path):
+    scene, _ = scenes.small_variant("fire", (37, 29), 8, 0.2)
+    rng = np.random.default_rng(3)
+    film = rng.random((29, 37, 4), dtype=np.float32)
+    film[0, 0] = [np.float32(np.inf), np.float32(np.nan), -0.0, 5.0]  # bit patterns survive, not just values
+    path = tmp_path / "render.film"
+    api.film_save(path, scene, film, 6)
+    assert not (tmp_path / "render.film.tmp").exists()
+    got, nxt = api.film_load(path, scene)
+    assert nxt == 6 and got.tobytes() == film.tobytes()
+    # a resumed render may ask for more waves / other worker counts: not part of the fingerprint
+    more = scene.copy(); more.num_waves = 64; more.num_workers = 3
+    assert api.film_load(path, more)[1] == 6
+    # anything that changes the film is: seed, camera, medium, tile size
+    for mutate in (lambda s: setattr(s, "seed", s.seed + 1), lambda s: s.tile_size.__setitem__(0, 4),
+                   lambda s: setattr(s.volume_parameters, "sigma_s", 0.5), lambda s: s.camera_parameters.position.__setitem__(1, 31.0)):
+        other = scene.copy(); mutate(other)
+        with pytest.raises(api.VptError) as e:
+            api.film_load(path, other)
+        assert e.value.code == -6 and "different scene" in str(e.value)
+    other = scene.copy(); other.output_size[0] = 36
+    with pytest.raises(api.VptError):
+        api.film_load(path, other)
+    # truncated and missing files are I/O errors; so is a file that is not a checkpoint
+    data = path.read_bytes()
+    (tmp_path / "cut.film").write_bytes(data[: len(data) // 2])
+    (tmp_path / "junk.film").write_bytes(b"not a film" * 10)
+    for name in ("cut.film", "junk.film", "missing.film"):
+        with pytest.raises(api.VptError) as e:
+            api.film_load(tmp_path / name, scene)
+        assert e.value.code == -5

@@ -91,7 +91,7 @@ EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_sample_grid", "vptc_film_to_image",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
-    "vptc_synth_volume", "vptc_write_png", "vptc_version",
+    "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
 ]
 
 _lib = None
@@ -133,6 +133,8 @@ def lib() -> C.CDLL:
     L.vptc_free.restype = None
     L.vptc_synth_volume.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.c_double, u32, C.POINTER(C.c_double), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]
     L.vptc_write_png.argtypes = [C.c_char_p, vp, C.c_int64, C.c_int64]
+    L.vptc_film_save.argtypes = [C.c_char_p, C.POINTER(Scene), vp, u32]
+    L.vptc_film_load.argtypes = [C.c_char_p, C.POINTER(Scene), vp, C.POINTER(u32)]
     _lib = L
     return L
 
@@ -219,6 +221,21 @@ def scene_from_json(text: str):
 def write_png(path, rgb: np.ndarray):
     rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
     _check(lib().vptc_write_png(str(path).encode(), _ptr(rgb), rgb.shape[1], rgb.shape[0]))
+
+
+def film_save(path, scene: "Scene", film: np.ndarray, next_wave: int):
+    """vptc_film_save: checkpoint of a progressive render (float4 film + the next wave to render)."""
+    film = np.ascontiguousarray(film, dtype=np.float32)
+    assert film.shape == (scene.height, scene.width, 4)
+    _check(lib().vptc_film_save(str(path).encode(), C.byref(scene), _ptr(film), int(next_wave)))
+
+
+def film_load(path, scene: "Scene"):
+    """vptc_film_load -> (film, next_wave); raises VptError when the file is missing/truncated or belongs to another scene."""
+    film = np.zeros((scene.height, scene.width, 4), np.float32)
+    nxt = C.c_uint32(0)
+    _check(lib().vptc_film_load(str(path).encode(), C.byref(scene), _ptr(film), C.byref(nxt)))
+    return film, int(nxt.value)
 
 
 # ---------------------------------------------------------------- the renderer

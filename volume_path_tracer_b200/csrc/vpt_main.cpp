@@ -6,9 +6,16 @@
 // "[FATAL]: ... ; exit(1)" error convention (include/vpt/logging.hpp:16). The jthread spawn + raylib
 // preview loop (main.cpp:63-134) is replaced by vptc_render calls; there is no window on this box, so the
 // image is saved when the last wave has finished instead of when the window closes (main.cpp:136-143).
-// Optional environment: VPT_DEVICE (CUDA device index, default 0), VPT_WAVES_PER_CALL (progress granularity).
+// Optional environment: VPT_DEVICE (CUDA device index, default 0), VPT_WAVES_PER_CALL (progress granularity, default 64).
+// Progressive semantics of the preview window, headless:
+//   VPT_SAVE_EVERY=K   rewrite the output image every K waves (the window's periodic redraw, main.cpp:107-131)
+//   VPT_CHECKPOINT=F   keep the float4 film + next wave in F (written whenever the image is, and at the end); when F
+//                      exists and matches the scene the render RESUMES from it — num_waves may have been raised since
+//   SIGINT / SIGTERM   = closing the window: finish the waves in flight, save image (+ checkpoint), exit 0
+//                      (TileProvider::stop_at_next_wave, tile_provider.cpp:107-110; main.cpp:133-143)
 #include <algorithm>
 #include <chrono>
+#include <csignal>
 #include <cstdlib>
 #include <filesystem>
 #include <iostream>
@@ -20,6 +27,9 @@
 #define vptFATAL(x) do { std::clog << "[FATAL]: " << x << "\n"; std::exit(1); } while (false)
 #define vptWARN(x) do { std::clog << "[WARN]: " << x << "\n"; } while (false)
 #define vptINFO(x) do { std::clog << "[INFO]: " << x << "\n"; } while (false)
+
+static volatile std::sig_atomic_t g_stop = 0;
+static void on_signal(int) { g_stop = 1; }
 
 int main(int argc, char* argv[])
 {
@@ -58,21 +68,44 @@ int main(int argc, char* argv[])
     const char* wpc_env = std::getenv("VPT_WAVES_PER_CALL");
     const uint32_t per_call = std::max(1, wpc_env ? std::atoi(wpc_env) : 64);
 
+    const char* every_env = std::getenv("VPT_SAVE_EVERY");
+    const uint32_t save_every = every_env ? uint32_t(std::max(0, std::atoi(every_env))) : 0u;
+    const char* ckpt = std::getenv("VPT_CHECKPOINT");
+    uint32_t first_wave = 1;
+    if (ckpt && std::filesystem::exists(ckpt)) {
+        uint32_t next = 1;
+        if (vptc_film_load(ckpt, &cfg, film.data(), &next) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+        first_wave = next;
+        vptINFO("Resuming from checkpoint " << ckpt << " at wave " << first_wave);
+    }
+    std::signal(SIGINT, on_signal);
+    std::signal(SIGTERM, on_signal);
+
+    std::vector<uint8_t> img(size_t(W) * size_t(H) * 3);
+    auto save = [&](uint32_t next_wave) {
+        if (vptc_film_to_image(ctx, film.data(), W, H, img.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+        if (vptc_write_png(output_path.c_str(), img.data(), W, H) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+        if (ckpt && vptc_film_save(ckpt, &cfg, film.data(), next_wave) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+    };
+
     const auto start = std::chrono::high_resolution_clock::now();
     double device_ms = 0.0;
-    for (uint32_t wave = 1; wave <= cfg.num_waves; wave += per_call) {
-        const uint32_t n = std::min(per_call, cfg.num_waves - wave + 1);
+    uint32_t wave = first_wave;
+    while (wave <= cfg.num_waves && !g_stop) {
+        uint32_t n = std::min(per_call, cfg.num_waves - wave + 1);
+        if (save_every) n = std::min(n, save_every - (wave - 1) % save_every); // calls end on multiples of K
         vptINFO("Starting wave " << wave << "/" << cfg.num_waves);
         if (vptc_render(ctx, &cfg, wave, n, film.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
         device_ms += vptc_last_render_ms(ctx);
+        wave += n;
+        if (save_every && (wave - 1) % save_every == 0 && wave <= cfg.num_waves) save(wave);
     }
+    if (g_stop && wave <= cfg.num_waves) vptINFO("Stopped at wave " << wave - 1 << "/" << cfg.num_waves);
     const auto elapsed = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - start);
+    const double rendered = double(W) * double(H) * double(wave - first_wave);
     vptINFO("Rendering complete in " << elapsed.count() << " ms (" << device_ms << " ms on the device, "
-            << double(W) * double(H) * double(cfg.num_waves) / (device_ms * 1e-3) / 1e6 << " M pixel-samples/s)");
-
-    std::vector<uint8_t> img(size_t(W) * size_t(H) * 3);
-    if (vptc_film_to_image(ctx, film.data(), W, H, img.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
-    if (vptc_write_png(output_path.c_str(), img.data(), W, H) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+            << (device_ms > 0.0 ? rendered / (device_ms * 1e-3) / 1e6 : 0.0) << " M pixel-samples/s)");
+    save(wave);
     vptc_destroy(ctx);
     return 0;
 }

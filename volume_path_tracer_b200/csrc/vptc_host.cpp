@@ -1,9 +1,11 @@
 // vptc_host.cpp — the host-only entry points of include/vptc.h (no CUDA calls here):
 // .nvdb I/O, synthetic volumes, scene JSON, PNG. The device side lives in vptc_device.cu.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <string>
+#include <vector>
 
 #include "host/json_scene.hpp"
 #include "host/nvdb_build.hpp"
@@ -107,6 +109,65 @@ int vptc_write_png(const char* path, const uint8_t* rgb8, int64_t width, int64_t
     std::string err;
     if (!vpt_host::write_png_rgb8(path, rgb8, width, height, err)) { set_global_error(err); return VPTC_ERR_IO; }
     return VPTC_OK;
+}
+
+// ---- film checkpoint ----
+namespace {
+struct FilmHeader { char magic[8]; uint32_t version; uint32_t next_wave; int64_t width, height; uint64_t fingerprint; };
+// FNV-1a over every scene field that determines the film, field by field (the POD has padding); num_waves and
+// num_workers are left out on purpose.
+uint64_t scene_fingerprint(const vptc_scene& s)
+{
+    uint64_t h = 1469598103934665603ULL;
+    auto mix = [&](const void* p, size_t n) { for (size_t i = 0; i < n; ++i) { h ^= static_cast<const unsigned char*>(p)[i]; h *= 1099511628211ULL; } };
+    mix(&s.seed, sizeof s.seed); mix(s.output_size, sizeof s.output_size); mix(s.tile_size, sizeof s.tile_size);
+    const vptc_camera_parameters& c = s.camera_parameters;
+    mix(c.position, sizeof c.position); mix(c.look, sizeof c.look); mix(c.up, sizeof c.up); mix(&c.vfov_deg, 4); mix(&c.imaging_ratio, 4);
+    const vptc_worker_parameters& w = s.worker_parameters;
+    mix(&w.single_pixel_enabled, 4); mix(w.single_pixel_coord, sizeof w.single_pixel_coord); mix(&w.use_jitter, 4);
+    mix(w.infinite_light.xyz, 12); mix(&w.infinite_light.multiplier, 4);
+    mix(w.distant_light.xyz, 12); mix(&w.distant_light.multiplier, 4); mix(w.distant_light.inv_direction, 12); mix(&w.max_depth, 4);
+    const vptc_volume_parameters& v = s.volume_parameters;
+    mix(&v.henyey_greenstein_g, 4); mix(&v.le_scale, 4); mix(&v.sigma_a, 4); mix(&v.sigma_s, 4); mix(&v.temperature_offset, 4); mix(&v.temperature_scale, 4);
+    return h;
+}
+const char kFilmMagic[8] = {'V', 'P', 'T', 'F', 'I', 'L', 'M', '1'};
+} // namespace
+
+int vptc_film_save(const char* path, const vptc_scene* scene, const float* film_xyzw, uint32_t next_wave)
+{
+    if (!path || !scene || !film_xyzw || scene->output_size[0] <= 0 || scene->output_size[1] <= 0) { set_global_error("vptc_film_save: bad argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    FilmHeader h{};
+    std::memcpy(h.magic, kFilmMagic, 8);
+    h.version = 1; h.next_wave = next_wave; h.width = scene->output_size[0]; h.height = scene->output_size[1]; h.fingerprint = scene_fingerprint(*scene);
+    const size_t n = size_t(h.width) * size_t(h.height) * 4;
+    const std::string tmp = std::string(path) + ".tmp";
+    std::FILE* f = std::fopen(tmp.c_str(), "wb");
+    if (!f) { set_global_error("vptc_film_save: cannot open " + tmp); return VPTC_ERR_IO; }
+    const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(film_xyzw, sizeof(float), n, f) == n;
+    const bool closed = std::fclose(f) == 0;
+    if (!ok || !closed || std::rename(tmp.c_str(), path) != 0) { std::remove(tmp.c_str()); set_global_error(std::string("vptc_film_save: write failed for ") + path); return VPTC_ERR_IO; }
+    return VPTC_OK;
+}
+
+int vptc_film_load(const char* path, const vptc_scene* scene, float* film_xyzw, uint32_t* next_wave)
+{
+    if (!path || !scene || !film_xyzw || !next_wave) { set_global_error("vptc_film_load: bad argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    std::FILE* f = std::fopen(path, "rb");
+    if (!f) { set_global_error(std::string("vptc_film_load: cannot open ") + path); return VPTC_ERR_IO; }
+    FilmHeader h{};
+    int rc = VPTC_OK;
+    if (std::fread(&h, sizeof h, 1, f) != 1 || std::memcmp(h.magic, kFilmMagic, 8) != 0 || h.version != 1) { set_global_error(std::string("vptc_film_load: not a film checkpoint: ") + path); rc = VPTC_ERR_IO; }
+    else if (h.width != scene->output_size[0] || h.height != scene->output_size[1] || h.fingerprint != scene_fingerprint(*scene)) {
+        set_global_error(std::string("vptc_film_load: checkpoint was written for a different scene: ") + path); rc = VPTC_ERR_CONFIG;
+    } else {
+        const size_t n = size_t(h.width) * size_t(h.height) * 4;
+        std::vector<float> buf(n); // the caller's film is only touched by a complete read
+        if (std::fread(buf.data(), sizeof(float), n, f) != n) { set_global_error(std::string("vptc_film_load: truncated checkpoint: ") + path); rc = VPTC_ERR_IO; }
+        else { std::memcpy(film_xyzw, buf.data(), n * sizeof(float)); *next_wave = h.next_wave; }
+    }
+    std::fclose(f);
+    return rc;
 }
 
 } // extern "C"
