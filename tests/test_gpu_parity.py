@@ -217,6 +217,84 @@ def test_edge_cases(renderer, oracle, api, scenes, loaded):
     assert np.allclose(film[..., :3], want[None, None, :], rtol=1e-6)
 
 
+def test_more_edge_cases(renderer, oracle, api, scenes, loaded):
+    """Corners of the parameter space the reference code branches on; the GPU must equal the oracle draw for draw."""
+    scene, spec, grids = loaded("fire")
+    vol = oracle.volume(grids)
+
+    def same(s, jids):
+        xo, no, _ = vol.trace_jobs(s, jids); xg, ng = renderer.trace_jobs(s, jids)
+        assert np.array_equal(no, ng)
+        assert rel_err(xo, xg).max() <= REL_TOL
+
+    some = np.arange(0, scene.ntiles * 2, 5, dtype=np.uint64)
+    # n_waves == 0 renders nothing; so does a wave range past num_waves' end — waves are only addresses (tile_provider.cpp:30)
+    film = renderer.new_film(scene)
+    renderer.run(scene, film, first_wave=1, n_waves=0)
+    assert not film.any()
+    renderer.run(scene, film, first_wave=1000, n_waves=1)
+    ref = np.zeros_like(film); vol.render(scene, ref, first_wave=1000, n_waves=1)
+    assert np.array_equal(film[..., 3], ref[..., 3]) and np.allclose(film, ref, rtol=1e-5, atol=1e-7)
+    # isotropic limit of the phase function: |g| < 1e-3 takes the `1 - 2u` branch (random.hpp:60-62)
+    s = scene.copy(); s.volume_parameters.henyey_greenstein_g = 5.0e-4
+    same(s, some)
+    # backward scattering, and a strongly forward lobe
+    for g in (-0.6, 0.95):
+        s = scene.copy(); s.volume_parameters.henyey_greenstein_g = g
+        same(s, some)
+    # max_depth == 0: the bounce loop never runs, every path is the infinite light (worker.cpp:130,198-200)
+    s = scene.copy(); s.worker_parameters.max_depth = 0
+    same(s, some)
+    film = renderer.run(s, renderer.new_film(s))
+    inf = np.array(s.worker_parameters.infinite_light.xyz, np.float32) * np.float32(s.worker_parameters.infinite_light.multiplier)
+    assert np.allclose(film[..., :3], (np.float32(s.camera_parameters.imaging_ratio) * inf * np.float32(s.num_waves))[None, None, :], rtol=1e-6)
+    # max_depth == 1: one bounce, then out of depth
+    s = scene.copy(); s.worker_parameters.max_depth = 1
+    same(s, some)
+    # purely absorbing medium (sigma_s = 0): every real collision terminates the path (worker.cpp:163-166)
+    s = scene.copy(); s.volume_parameters.sigma_s = 0.0
+    same(s, some)
+    # camera INSIDE the volume: rays start in the middle of the grid (Ray::clip with t0 inside the box)
+    s = scene.copy()
+    s.camera_parameters.position[0], s.camera_parameters.position[1], s.camera_parameters.position[2] = 0.5, 20.0, 0.25
+    same(s, some)
+    # a tile larger than the image: one job is the whole frame, clipped (tile_provider.cpp:69-85)
+    s = scene.copy()
+    s.output_size[0], s.output_size[1] = 21, 13
+    s.tile_size[0], s.tile_size[1] = 32, 32
+    assert s.ntiles == 1
+    same(s, np.arange(3, dtype=np.uint64))
+    film = renderer.run(s, renderer.new_film(s))
+    assert (film[..., 3] == s.num_waves).all()
+    # an axis-parallel view direction: zero direction components, the HDDA's dir == 0 arms (HDDA.h:60-75)
+    s = scene.copy()
+    s.camera_parameters.position[0], s.camera_parameters.position[1], s.camera_parameters.position[2] = 120.0, 30.0, 0.0
+    s.camera_parameters.look[0], s.camera_parameters.look[1], s.camera_parameters.look[2] = 0.0, 30.0, 0.0
+    s.worker_parameters.use_jitter = 0
+    s.output_size[0], s.output_size[1] = 33, 33  # odd size: the centre pixel looks exactly along -x
+    s.tile_size[0], s.tile_size[1] = 8, 8
+    same(s, np.arange(s.ntiles, dtype=np.uint64))
+
+
+def test_tiny_volume_mostly_missed(renderer, oracle, api, scenes, loaded):
+    """A volume of a handful of leaves far smaller than the view: most rays miss the grid's bounding box
+    (Volume::intersect -> nullopt, volume.cpp:84-86), the rest cross one or two nodes."""
+    scene, spec, grids = loaded("fire")
+    tiny = api.synth_volume("torus", (12, 12, 12), 1.0, 1, None)
+    try:
+        renderer.set_volume(tiny)
+        vol = oracle.volume(tiny)
+        s = scene.copy()
+        s.camera_parameters.look[0], s.camera_parameters.look[1], s.camera_parameters.look[2] = 0.0, 0.0, 0.0
+        s.camera_parameters.position[0], s.camera_parameters.position[1], s.camera_parameters.position[2] = 60.0, 10.0, 5.0
+        jids = np.arange(0, s.ntiles * 2, dtype=np.uint64)
+        xo, no, co = vol.trace_jobs(s, jids); xg, ng = renderer.trace_jobs(s, jids)
+        assert np.array_equal(no, ng) and rel_err(xo, xg).max() <= REL_TOL
+        assert co.density_evals > 0 and (no[:, 1:] - no[:, :-1] == 2).any()  # some paths sample the medium; many draw only their 2 jitters
+    finally:
+        renderer.set_volume(grids)
+
+
 def test_density_only_volume_skips_emission(renderer, oracle, api, loaded):
     """No temperature grid => the emission term is skipped entirely (worker.cpp:152)."""
     scene, spec, grids = loaded("fire")

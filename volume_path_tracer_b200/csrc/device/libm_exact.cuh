@@ -101,21 +101,19 @@ VPT_HD uint32_t abstop12(float x) { return (as_u32(x) >> 20) & 0x7ffu; }
 VPT_HD void sincosf_exact(float y, float& s_out, float& c_out)
 {
     double x = double(y);
-    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) { // |y| < pi/4
-        const double x2 = x * x;
-        if (abstop12(y) < abstop12(0x1p-12f)) { s_out = y; c_out = 1.0f; return; }
-        s_out = sincos_poly(x, x2, false, 0);
-        c_out = sincos_poly(x, x2, false, 1);
-        return;
-    }
+    // Branch-free form for SIMT: glibc's |y| < pi/4 shortcut is the general path with n = 0 (x - 0 * pi/2 == x, sign +1,
+    // table 0), and sincosf_poly evaluates BOTH polynomials and swaps them when n is odd — so one straight-line sequence
+    // serves every quadrant; only the |y| < 2^-12 early-out stays, as a select.
     const double r = x * 0x1.45F306DC9C883p+23; // 2/pi * 2^24
-    const int n = (int32_t(r) + 0x800000) >> 24;
+    const int n = abstop12(y) < abstop12(0x1.921FB6p-1f) ? 0 : (int32_t(r) + 0x800000) >> 24;
     x = x - double(n) * 0x1.921FB54442D18p0;
     const double sgn = ((n + 1) & 2) ? -1.0 : 1.0; // sign[n & 3] = {1, -1, -1, 1}
     const bool neg = (n & 2) != 0;
     const double xs = x * sgn, x2 = x * x;
-    s_out = sincos_poly(xs, x2, neg, n);
-    c_out = sincos_poly(xs, x2, neg, n ^ 1);
+    const float sp = sincos_poly(xs, x2, neg, 0), cp = sincos_poly(xs, x2, neg, 1);
+    const bool odd = (n & 1) != 0, tiny = abstop12(y) < abstop12(0x1p-12f);
+    s_out = tiny ? y : (odd ? cp : sp);
+    c_out = tiny ? 1.0f : (odd ? sp : cp);
 }
 
 } // namespace vptm

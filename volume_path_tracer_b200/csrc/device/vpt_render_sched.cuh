@@ -24,6 +24,9 @@ namespace vptd {
 // lanes and the kernel 25 % slower (profiles/r01_codegen_cliff.txt). -DVPT_SYNC_SETUP=1 pins the rejoin with a
 // __syncwarp over the lanes that entered the stage; it costs ~1 % when the compiler already does the right thing
 // (the present code), so it is off — turn it on first when an edit to SETUP slows the kernel unexpectedly.
+#ifndef VPT_HOT_REPS
+#define VPT_HOT_REPS 2 // HOT passes per scheduling decision: halves the ballot/threshold overhead per HDDA step (+4..7 %, profiles/r01_codegen_cliff.txt)
+#endif
 #ifndef VPT_SYNC_SETUP
 #define VPT_SYNC_SETUP 0
 #endif
@@ -192,6 +195,10 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         // ------------------------------------------------------------ HOT: one HDDA step and/or one free-flight draw
 #if VPT_SYNC_HOT
         const unsigned hot_mask = __ballot_sync(FULL, run_hot && stage == ST_HOT);
+#endif
+#if VPT_HOT_REPS > 1
+#pragma unroll 1
+        for (int rep = 0; rep < VPT_HOT_REPS; ++rep) // several HOT passes per scheduling decision (A/B switch)
 #endif
         if (run_hot && stage == ST_HOT) {
             if (!m.has_seg) { // RayMajorantIterator::next, one step   volume.cpp:53-71
