@@ -5,11 +5,12 @@
 // its divisions and square roots, HG sampling, camera ray; the trilinear fetch + collision logic) run with
 // 1.6-3 lanes and account for ~45 % of all issued warp instructions — almost every iteration finds at least
 // ONE of the 32 lanes needing them. Here a lane carries an explicit stage
-//     SETUP -> DDA -> SAMPLE -> EVAL (-> SAMPLE | SETUP)
+//     SETUP -> HOT (HDDA steps and free-flight draws) -> EVAL (-> HOT | SETUP)
 // and each loop iteration runs a stage only if enough lanes are queued for it (ballot + popc against a per-stage
-// threshold) or it is the most populated one (progress guarantee). Lanes queued for a stage that is skipped
-// simply wait; the arithmetic and its order per lane are unchanged, so results stay bit-identical to variant 1.
-// This is the in-register, in-warp form of wavefront regrouping: no path state ever goes to memory.
+// threshold) or it is the most populated one (progress guarantee); HOT runs VPT_HOT_REPS passes per decision. Lanes
+// queued for a stage that is skipped simply wait; the arithmetic and its order per lane are unchanged, so results
+// stay bit-identical to variant 1. This is the in-register, in-warp form of wavefront regrouping: the hot path
+// state never goes to memory (the cold part sits in shared memory, see below).
 #pragma once
 #include "vpt_render_flat.cuh"
 
@@ -19,19 +20,16 @@ namespace vptd {
 #define VPT_SCHED_MIN_BLOCKS 7 // resident 128-thread blocks per SM the register allocation must allow (72 registers)
 #endif
 
-// Explicit reconvergence points (A/B switches). The kernel's speed hangs on where ptxas lets the lanes of a stage
+// Explicit reconvergence point (A/B switch). The kernel's speed hangs on where ptxas lets the lanes of a stage
 // rejoin: an edit as small as one conditional load in the job fetch made SETUP's ray begin run at 4.5 instead of 7.7
 // lanes and the kernel 25 % slower (profiles/r01_codegen_cliff.txt). -DVPT_SYNC_SETUP=1 pins the rejoin with a
 // __syncwarp over the lanes that entered the stage; it costs ~1 % when the compiler already does the right thing
 // (the present code), so it is off — turn it on first when an edit to SETUP slows the kernel unexpectedly.
 #ifndef VPT_HOT_REPS
-#define VPT_HOT_REPS 2 // HOT passes per scheduling decision: halves the ballot/threshold overhead per HDDA step (+4..7 %, profiles/r01_codegen_cliff.txt)
+#define VPT_HOT_REPS 3 // HOT passes per scheduling decision: cuts the ballot/threshold overhead per HDDA step (+4..7 %, profiles/r01_codegen_cliff.txt)
 #endif
 #ifndef VPT_SYNC_SETUP
 #define VPT_SYNC_SETUP 0
-#endif
-#ifndef VPT_SYNC_HOT
-#define VPT_SYNC_HOT 0 // same for HOT's two halves; measured -8 %, kept for experiments only
 #endif
 enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
 
@@ -55,7 +53,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     CellCache cc;
     cc.reset();
     March m;
-    m.has_seg = false;
+    enum : int { M_STEP = 0, M_PEND = 1, M_DRAW = 2 }; // marching: step next / majorant fetch in flight; drawing in a closed segment
+    int mode = M_STEP;
     float pend_u = 0.0f;
     bool shadow = false, pixel_open = false;
     int stage = ST_SETUP, sub = PH_NEXT_PIXEL;
@@ -185,7 +184,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     const RayDir rdir = shadow ? shadow_dir : make_ray_dir(G, rd);
                     if (flat_begin_ray_dir<COUNT>(m, G, cc, CLD3(C_POS), rdir, ray_done, st)) {
                         if (ray_done) VPT_RAY_FINISHED();
-                        else stage = ST_HOT;
+                        else { stage = ST_HOT; mode = M_STEP; }
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
                     else { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; }
                 }
@@ -193,35 +192,25 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
 
         // ------------------------------------------------------------ HOT: one HDDA step and/or one free-flight draw
-#if VPT_SYNC_HOT
-        const unsigned hot_mask = __ballot_sync(FULL, run_hot && stage == ST_HOT);
-#endif
 #if VPT_HOT_REPS > 1
 #pragma unroll 1
         for (int rep = 0; rep < VPT_HOT_REPS; ++rep) // several HOT passes per scheduling decision (A/B switch)
 #endif
+        // Software-pipelined: a pass CONSUMES the majorant whose fetch the previous pass issued, draws if a segment closed,
+        // then takes the next HDDA step and ISSUES that voxel's fetch — the L2 latency of the slot load (the kernel's top
+        // stall: 10 % of all stall samples at `majorant != seg_dmaj`) overlaps the draw, the prefilter and the loop
+        // overhead instead of sitting between the step and its use. Same operations per lane in the same order.
         if (run_hot && stage == ST_HOT) {
-            if (!m.has_seg) { // RayMajorantIterator::next, one step   volume.cpp:53-71
-                bool closed;
-                if (!hdda_step_bf(m)) { m.seg_t1 = m.t1; closed = true; }
-                else {
-                    const V3 p = m.at(m.t0 + 1.0001f);
-                    hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
-                    m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
-                    if (COUNT) ++st.majorant_fetches;
-                    closed = m.majorant != m.seg_dmaj;
-                    if (closed) m.seg_t1 = m.t0;
-                }
-                if (closed) {
-                    if (m.seg_dmaj > 0.0f) m.has_seg = true;
+            if (mode == M_PEND) { // RayMajorantIterator::next after the step: volume.cpp:60-70
+                mode = M_STEP;
+                if (m.majorant != m.seg_dmaj) {                 // NaN after a failed step: the segment closes at t1
+                    m.seg_t1 = fminf(m.t0, m.t1);               // t0 on a successful step (t0 <= t1), t1 when the step left the ray
+                    if (m.seg_dmaj > 0.0f) mode = M_DRAW;
                     else if (m.t0 >= m.t1) VPT_RAY_FINISHED();         // empty segment dropped, iterator.next() -> nullopt
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
                 }
             }
-#if VPT_SYNC_HOT
-            __syncwarp(hot_mask);
-#endif
-            if (m.has_seg && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
+            if (mode == M_DRAW && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
                 pend_u = rng.uniform();
                 // ~85 % of the draws overshoot the segment. Only the DECISION `t < seg.t1` matters then, not t itself, so
                 // a conservative test with the SFU approximations (MUFU.LG2 / RCP, error margins far above their
@@ -230,12 +219,38 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
                 const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
                 if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
-                    m.has_seg = false;
+                    mode = M_STEP;
+                    if (m.t0 >= m.t1) VPT_RAY_FINISHED();
+                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
+                } else stage = ST_EVAL;
+            }
+            if (mode == M_STEP && stage == ST_HOT) { // one HDDA step, majorant fetch issued   volume.cpp:53-59
+                if (!hdda_step_bf(m)) m.majorant = __int_as_float(0x7fc00000);
+                else {
+                    const V3 p = m.at(m.t0 + 1.0001f);
+                    hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
+                    m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
+                    if (COUNT) ++st.majorant_fetches;
+                }
+                mode = M_PEND;
+            }
+        }
+            if (mode == M_DRAW && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
+                pend_u = rng.uniform();
+                // ~85 % of the draws overshoot the segment. Only the DECISION `t < seg.t1` matters then, not t itself, so
+                // a conservative test with the SFU approximations (MUFU.LG2 / RCP, error margins far above their
+                // documented bounds) settles the clear cases; everything else — the hits and the ~0.1 % near the
+                // boundary — goes to EVAL, which evaluates t exactly (glibc-exact logf, IEEE divisions) and decides.
+                const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
+                const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
+                if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
+                    mode = M_STEP;
                     if (m.t0 >= m.t1) VPT_RAY_FINISHED();
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
                 } else stage = ST_EVAL;
             }
         }
+#endif
         // ------------------------------------------------------------ EVAL: trilinear density + collision   worker.cpp:68-84,148-188
         if (run_eval && stage == ST_EVAL) {
             const float sigma_maj = m.seg_dmaj * S.sigma_t;
@@ -251,7 +266,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 density = trilinear_cached(G, cc, p.x, p.y, p.z);
                 if (density > 0.0f) pos_idx = p;
             } else { // overshoot after all: segment dropped, iterator.next()
-                m.has_seg = false;
+                mode = M_STEP;
                 if (m.t0 >= m.t1) VPT_RAY_FINISHED();
                 else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
             }
