@@ -235,22 +235,6 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 mode = M_PEND;
             }
         }
-            if (mode == M_DRAW && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
-                pend_u = rng.uniform();
-                // ~85 % of the draws overshoot the segment. Only the DECISION `t < seg.t1` matters then, not t itself, so
-                // a conservative test with the SFU approximations (MUFU.LG2 / RCP, error margins far above their
-                // documented bounds) settles the clear cases; everything else — the hits and the ~0.1 % near the
-                // boundary — goes to EVAL, which evaluates t exactly (glibc-exact logf, IEEE divisions) and decides.
-                const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
-                const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
-                if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
-                    mode = M_STEP;
-                    if (m.t0 >= m.t1) VPT_RAY_FINISHED();
-                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
-                } else stage = ST_EVAL;
-            }
-        }
-#endif
         // ------------------------------------------------------------ EVAL: trilinear density + collision   worker.cpp:68-84,148-188
         if (run_eval && stage == ST_EVAL) {
             const float sigma_maj = m.seg_dmaj * S.sigma_t;
