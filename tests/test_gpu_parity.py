@@ -374,14 +374,14 @@ def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
 
 @pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
 def test_kernel_variants_agree(renderer, loaded, name):
-    """The nested (0), flat (1) and stage-scheduled (2) megakernels are three schedules of the same arithmetic:
-    per-job radiance, RNG draw counts and work counters must be bit-identical."""
+    """The nested (0), flat (1), stage-scheduled (2) and job-pool (3) megakernels are four schedules of the same
+    arithmetic: per-job radiance, RNG draw counts and work counters must be bit-identical."""
     scene, spec, grids = loaded(name)
     jids = np.arange(scene.ntiles * scene.num_waves, dtype=np.uint64)
     res = []
     try:
         renderer.enable_counters(True)
-        for v in (0, 1, 2):
+        for v in (0, 1, 2, 3):
             renderer.set_kernel_variant(v)
             x, n = renderer.trace_jobs(scene, jids)
             f = renderer.run(scene, renderer.new_film(scene))

@@ -11,6 +11,9 @@ if os.environ.get("WAVES"):  # override the waves per launch of every case
     cases = [(n, f, int(os.environ["WAVES"])) for n, f, _ in cases]
 if os.environ.get("CASES"):
     cases = [c for c in cases if c[0] in os.environ["CASES"].split(",")]
+pools = os.environ.get("POOL", "").split(";") if os.environ.get("POOL") else [None]  # variant 3: "3,20;2,16" = HOT passes, min HOT lanes
+if pools != [None]:
+    threshes = pools
 for name, factor, waves in cases:
     scene, spec = scenes.load_config(name)
     if factor != 1.0:
@@ -20,7 +23,7 @@ for name, factor, waves in cases:
     ps = scene.width * scene.height * waves
     for th in threshes:
         if th:
-            os.environ["VPT_SCHED_THRESH"] = th
+            os.environ["VPT_POOL_PARAMS" if pools != [None] else "VPT_SCHED_THRESH"] = th
         r = api.Renderer(0)
         r.set_volume(g)
         for v in variants:

@@ -3,7 +3,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["VPT_SCHED_STATS"] = "1"
 import torch
 from volume_path_tracer_b200 import api, scenes
-for name, factor, waves in [("dense512", 1.0, 16), ("wdas_cloud", 0.25, 16), ("fire", 1.0, 32)]:
+for name, factor, waves in [("dense512", 1.0, int(os.environ.get("SWAVES", 16))), ("wdas_cloud", 0.25, int(os.environ.get("SWAVES", 16))), ("fire", 1.0, 32)]:
     scene, spec = scenes.load_config(name)
     if factor != 1.0: spec = spec.scaled(factor)
     g = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)

@@ -149,6 +149,7 @@ __device__ __forceinline__ void film_add(float* film, float x, float y, float z)
 } // namespace vptd
 #include "vpt_render_flat.cuh"  // variant 1: the flat state-machine megakernel
 #include "vpt_render_sched.cuh" // variant 2: flat + warp-level stage scheduling
+#include "vpt_render_pool.cuh"  // variant 3: per-warp job pool in shared memory
 namespace vptd {
 
 // ---------------------------------------------------------------- variant 0: the first, nested megakernel (kept for the ncu comparison)
@@ -260,7 +261,8 @@ static void launch_variant(const RenderArgs& args, int variant, int grid_blocks,
 {
     if (variant == 0) vpt_render_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
     else if (variant == 1) vpt_render_flat_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-    else vpt_render_sched_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else if (variant == 2) vpt_render_sched_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else vpt_render_pool_kernel<TRACE, COUNT><<<grid_blocks, POOL_THREADS, pool_smem_bytes<TRACE, COUNT>(), stream>>>(args);
 }
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream)
 {
@@ -272,11 +274,16 @@ template <bool TRACE, bool COUNT>
 static int occupancy_variant(int variant)
 {
     int n = 0;
+    if (variant == 3) { // the pool needs more than the default 48 KB of dynamic shared memory: opt in (idempotent)
+        if (cudaFuncSetAttribute(vpt_render_pool_kernel<TRACE, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pool_smem_bytes<TRACE, COUNT>())) != cudaSuccess) return 0;
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_pool_kernel<TRACE, COUNT>, POOL_THREADS, pool_smem_bytes<TRACE, COUNT>()) == cudaSuccess ? n : 0;
+    }
     const cudaError_t e = variant == 0   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
                           : variant == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_flat_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
                                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0);
     return e == cudaSuccess ? n : 0;
 }
+int render_jobs_per_block(int variant) { return variant == 3 ? POOL_JOBS_PER_BLOCK : VPT_BLOCK_THREADS; }
 int render_blocks_per_sm(int variant, bool trace, bool count)
 {
     if (trace) return count ? occupancy_variant<true, true>(variant) : occupancy_variant<true, false>(variant);

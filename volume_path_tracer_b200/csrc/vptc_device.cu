@@ -43,6 +43,7 @@ struct vptc_ctx {
     bool count = false;
     int variant = 2; // render kernel variant (vptc_set_kernel_variant)
     int sched_thresh[4] = {12, 8, 8, 16};
+    int pool_params[4] = {3, 8, 28, 28}; // variant 3: HOT passes per scheduling decision; queued slots needed to run HOT / EVAL / SETUP
     float last_ms = 0.0f;
     vptc_counters last_counters{};
     int num_sms = 0;
@@ -110,13 +111,19 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     for (int i = 0; i < 4; ++i) A.sched_thresh[i] = std::max(1, ctx->sched_thresh[i]); // the kernel relies on >= 1
     CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
-    const int per_sm = render_blocks_per_sm(ctx->variant, trace, ctx->count);
+    for (int i = 0; i < 4; ++i) A.pool_params[i] = ctx->pool_params[i];
+    for (int i = 0; i < 4; ++i) A.pool_params[i] = std::max(1, A.pool_params[i]);
+    // variant 3 packs pixel coordinates into 16-bit halves of its slot words: larger frames / tiles take variant 2
+    const int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
+    int per_sm = render_blocks_per_sm(variant, trace, ctx->count);
+    if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
     // persistent grid: every SM filled to its occupancy limit, never more blocks than jobs need
-    unsigned long long want = (A.n_jobs + VPT_BLOCK_THREADS - 1) / VPT_BLOCK_THREADS;
+    const unsigned long long per_block = (unsigned long long)(render_jobs_per_block(variant));
+    unsigned long long want = (A.n_jobs + per_block - 1) / per_block;
     int blocks = int(std::min<unsigned long long>(want ? want : 1ULL, (unsigned long long)(ctx->num_sms) * per_sm));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_render(A, ctx->variant, trace, ctx->count, blocks, ctx->stream));
+    CU(launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     CU(cudaEventSynchronize(ctx->ev1));
     CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
@@ -168,7 +175,9 @@ int vptc_create(vptc_ctx** out, int device)
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
     CU(upload_cie_table(vpt_host::cie_table()));
-    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(2, std::max(0, std::atoi(v)));
+    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(3, std::max(0, std::atoi(v)));
+    if (const char* v = std::getenv("VPT_POOL_PARAMS")) // "HOT passes,HOT slots,EVAL slots,SETUP slots" (tuning aid)
+        std::sscanf(v, "%d,%d,%d,%d", &ctx->pool_params[0], &ctx->pool_params[1], &ctx->pool_params[2], &ctx->pool_params[3]);
     if (const char* v = std::getenv("VPT_SCHED_THRESH")) // "setup,dda,sample,eval" lanes (tuning aid)
         std::sscanf(v, "%d,%d,%d,%d", &ctx->sched_thresh[0], &ctx->sched_thresh[1], &ctx->sched_thresh[2], &ctx->sched_thresh[3]);
     *out = c.release();
@@ -271,7 +280,7 @@ int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 int vptc_set_kernel_variant(vptc_ctx* ctx, int variant)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: ctx is null");
-    if (variant < 0 || variant > 2) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat) or 2 (flat + stage scheduling)");
+    if (variant < 0 || variant > 3) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat), 2 (flat + stage scheduling) or 3 (per-warp job pool)");
     ctx->variant = variant;
     return VPTC_OK;
 }
