@@ -141,6 +141,14 @@ VPTC_API int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint6
 VPTC_API int vptc_trace_segments(vptc_ctx* ctx, const float* origins_xyz, const float* dirs_xyz, size_t n_rays,
                                  uint32_t max_segs, float* segs_t0_t1_dmaj, uint32_t* n_segs);
 
+/* Debug front-end = Volume::log_majorant_trace (volume.cpp:176-192) as the reference's ray_visualizer drives it, headless:
+ * traces the UN-JITTERED camera ray through the centre of pixel (px, py) on the device and writes `csv_path` with the
+ * reference's columns X0,Y0,Z0,X1,Y1,Z1,T0,T1,Majorant — index-space end points of each merged majorant segment
+ * (world_to_density_index(ray.eval(t * idx_to_world_scale))), world-space T0/T1, and d_maj — so scripts/plot_majorant_trace.py
+ * keeps working. A ray that misses the volume writes the header only. (log_dda_trace's NodeInfo columns need the NanoVDB
+ * tree itself and stay with the oracle.) */
+VPTC_API int vptc_trace_pixel_csv(vptc_ctx* ctx, const vptc_scene* scene, int64_t px, int64_t py, const char* csv_path);
+
 /* Parity hook for the trilinear sampler (SampleFromVoxels<Acc,1>): grid 0 = density, 1 = temperature;
  * index-space positions. Also returns getDim/majorant per position when the pointers are non-NULL. */
 VPTC_API int vptc_sample_grid(vptc_ctx* ctx, int grid, const float* index_xyz, size_t n, float* values,

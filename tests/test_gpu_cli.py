@@ -128,3 +128,44 @@ def test_cli_sigint_stops_at_a_wave_boundary_and_saves(api, scenes, tmp_path):
     scene, _ = api.read_configuration(p)
     film, nxt = api.film_load(ck, scene)
     assert nxt > 9 and (nxt - 1) % 4 == 0 and (film[..., 3] == nxt - 1).all()
+
+
+@pytest.mark.gpu
+def test_cli_trace_pixel_writes_the_majorant_trace_csv(api, scenes, oracle, tmp_path):
+    """VPT_TRACE_PIXEL=x,y = Volume::log_majorant_trace (volume.cpp:176-192) for the pixel-centre camera ray: the
+    reference's columns, T0/T1/Majorant equal to the oracle's segment iterator (times scaled to world units), end
+    points = world_to_density_index(ray.eval(t)), segments contiguous; a pixel that misses the volume gives the header only."""
+    grids = api.synth_volume("fire", (50, 60, 50), 1.0, 1, None)
+    (tmp_path / "volumes").mkdir()
+    grids.write(tmp_path / "volumes" / "fire.nvdb")
+    scene_path = _scene(scenes, tmp_path, "../volumes/fire.nvdb", waves=1)
+    scene, _ = api.read_configuration(scene_path)
+    px, py = scene.width // 2, scene.height // 2
+    env = dict(os.environ, VPT_TRACE_PIXEL=f"{px},{py}")
+    r = subprocess.run([str(VPT), str(scene_path), str(tmp_path / "o.png")], capture_output=True, text=True, timeout=300, env=env, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    lines = (tmp_path / "majorant_trace.csv").read_text().strip().split("\n")
+    assert lines[0] == "X0,Y0,Z0,X1,Y1,Z1,T0,T1,Majorant"
+    rows = np.array([[float(v) for v in ln.split(",")] for ln in lines[1:]], np.float64)
+    o, d = oracle.camera_rays(scene, [px], [py], [0.0], [0.0])
+    vol = oracle.volume(grids)
+    segs, n = vol.trace_segments(o, d, 256)
+    assert n[0] >= 2 and len(rows) == n[0]
+    # idx_to_world_scale of this (uniform-voxel) grid = voxel size; compare world-space times and majorants
+    ratio = rows[:, 6] / segs[0, : n[0], 0].astype(np.float64)
+    assert np.allclose(ratio, ratio[0], rtol=1e-6) and np.allclose(rows[:, 7], segs[0, : n[0], 1].astype(np.float64) * ratio[0], rtol=1e-6)
+    assert np.array_equal(rows[:, 8].astype(np.float32), segs[0, : n[0], 2])
+    assert np.allclose(rows[1:, 0:3], rows[:-1, 3:6], atol=1e-3)  # each segment starts where the previous one ended
+    # the end points lie on the index-space ray: trilinear probes there agree with the oracle's at the same points
+    mid = (rows[:, 0:3] + rows[:, 3:6]) / 2
+    lo, hi = np.array([0, 0, 0]) - 1.0, np.array([50, 60, 50]) + 1.0
+    assert ((mid > lo - 64) & (mid < hi + 64)).all()
+    env["VPT_TRACE_PIXEL"] = "0,0"  # a corner pixel misses this small volume
+    r = subprocess.run([str(VPT), str(scene_path), str(tmp_path / "o.png")], capture_output=True, text=True, timeout=300, env=env, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    o, d = oracle.camera_rays(scene, [0], [0], [0.0], [0.0])
+    assert vol.trace_segments(o, d, 256)[1][0] == 0
+    assert (tmp_path / "majorant_trace.csv").read_text().strip() == "X0,Y0,Z0,X1,Y1,Z1,T0,T1,Majorant"
+    env["VPT_TRACE_PIXEL"] = "nonsense"
+    r = subprocess.run([str(VPT), str(scene_path), str(tmp_path / "o.png")], capture_output=True, text=True, timeout=300, env=env, cwd=tmp_path)
+    assert r.returncode == 1 and "[FATAL]" in r.stderr

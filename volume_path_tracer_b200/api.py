@@ -89,7 +89,7 @@ class VptError(RuntimeError):
 
 EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms",
-    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_sample_grid", "vptc_film_to_image",
+    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_sample_grid", "vptc_film_to_image",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
 ]
@@ -123,6 +123,7 @@ def lib() -> C.CDLL:
     L.vptc_set_kernel_variant.argtypes = [vp, C.c_int]
     L.vptc_trace_jobs.argtypes = [vp, C.POINTER(Scene), vp, sz, vp, vp]
     L.vptc_trace_segments.argtypes = [vp, vp, vp, sz, u32, vp, vp]
+    L.vptc_trace_pixel_csv.argtypes = [vp, C.POINTER(Scene), C.c_int64, C.c_int64, C.c_char_p]
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.vptc_film_to_image.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
     L.vptc_scene_from_json_file.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
@@ -305,6 +306,10 @@ class Renderer:
         n = np.zeros(len(o), np.uint32)
         _check(lib().vptc_trace_segments(self._ctx, _ptr(o), _ptr(d), len(o), max_segs, _ptr(segs), _ptr(n)), self._ctx)
         return segs, n
+
+    def trace_pixel_csv(self, scene, px: int, py: int, path):
+        """majorant_trace.csv of the pixel-centre camera ray (Volume::log_majorant_trace, volume.cpp:176-192)."""
+        _check(lib().vptc_trace_pixel_csv(self._ctx, C.byref(scene), int(px), int(py), str(path).encode()), self._ctx)
 
     def sample_grid(self, grid: int, index_xyz):
         p = np.ascontiguousarray(index_xyz, dtype=np.float32).reshape(-1, 3)

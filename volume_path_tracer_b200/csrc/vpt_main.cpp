@@ -11,11 +11,14 @@
 //   VPT_SAVE_EVERY=K   rewrite the output image every K waves (the window's periodic redraw, main.cpp:107-131)
 //   VPT_CHECKPOINT=F   keep the float4 film + next wave in F (written whenever the image is, and at the end); when F
 //                      exists and matches the scene the render RESUMES from it — num_waves may have been raised since
+//   VPT_TRACE_PIXEL=x,y  also write ./majorant_trace.csv for that pixel's centre ray (Volume::log_majorant_trace, volume.cpp:176-192:
+//                      the ray_visualizer's CSV for scripts/plot_majorant_trace.py), from the device's own segment iterator
 //   SIGINT / SIGTERM   = closing the window: finish the waves in flight, save image (+ checkpoint), exit 0
 //                      (TileProvider::stop_at_next_wave, tile_provider.cpp:107-110; main.cpp:133-143)
 #include <algorithm>
 #include <chrono>
 #include <csignal>
+#include <cstdio>
 #include <cstdlib>
 #include <filesystem>
 #include <iostream>
@@ -62,6 +65,12 @@ int main(int argc, char* argv[])
     if (vptc_create(&ctx, dev_env ? std::atoi(dev_env) : 0) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
     if (vptc_set_volume(ctx, density, density_bytes, temperature, temperature_bytes) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
     vptc_free(density); vptc_free(temperature); // the library baked its own copy
+    if (const char* tp = std::getenv("VPT_TRACE_PIXEL")) {
+        long long tx = -1, ty = -1;
+        if (std::sscanf(tp, "%lld,%lld", &tx, &ty) != 2) vptFATAL("VPT_TRACE_PIXEL must be \"x,y\"");
+        if (vptc_trace_pixel_csv(ctx, &cfg, tx, ty, "majorant_trace.csv") != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+        vptINFO("Wrote majorant_trace.csv for pixel (" << tx << ", " << ty << ")");
+    }
 
     const int64_t W = cfg.output_size[0], H = cfg.output_size[1];
     std::vector<float> film(size_t(W) * size_t(H) * 4, 0.0f);

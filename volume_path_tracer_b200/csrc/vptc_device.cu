@@ -1,6 +1,7 @@
 // vptc_device.cu — the device-facing entry points of include/vptc.h: context, volume staging, render,
 // parity hooks. Plain CUDA runtime; no torch types cross this boundary.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -345,6 +346,54 @@ int vptc_trace_segments(vptc_ctx* ctx, const float* origins, const float* dirs, 
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cleanup();
     if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_segments: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+int vptc_trace_pixel_csv(vptc_ctx* ctx, const vptc_scene* scene, int64_t px, int64_t py, const char* csv_path)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_pixel_csv: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (!csv_path) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_pixel_csv: csv_path is null");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (px < 0 || py < 0 || px >= scene->output_size[0] || py >= scene->output_size[1]) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_pixel_csv: pixel outside the image");
+    SceneDev S;
+    vpt_host::prepare_scene(*scene, ctx->has_temperature, S);
+    // Camera::generate_ray (camera.hpp:14-23) with sample offset 0: the kernels' arithmetic, on the host (-ffp-contract=off)
+    auto sum3 = [](float a, float b, float c) { return a + (b + c); };
+    const float rx = float(px) + 0.5f, ry = float(py) + 0.5f;
+    float d[3], o[3] = {S.cam_pos[0], S.cam_pos[1], S.cam_pos[2]};
+    for (int r = 0; r < 3; ++r) d[r] = sum3(S.cam_m[r * 3] * rx, S.cam_m[r * 3 + 1] * ry, S.cam_m[r * 3 + 2] * 0.0f) + S.cam_t[r];
+    const float nrm = std::sqrt(sum3(d[0] * d[0], d[1] * d[1], d[2] * d[2]));
+    for (int r = 0; r < 3; ++r) d[r] /= nrm;
+    uint32_t n = 0;
+    std::vector<float> segs(3);
+    if (int rc = vptc_trace_segments(ctx, o, d, 1, 1, segs.data(), &n)) return rc; // count first, then fetch them all
+    if (n > 1) { segs.assign(size_t(n) * 3, 0.0f); if (int rc = vptc_trace_segments(ctx, o, d, 1, n, segs.data(), &n)) return rc; }
+    // idx_to_world_scale (volume.cpp:91) and world_to_density_index (volume.cpp:172-174), NanoVDB's float map chains (Math.h:905-939)
+    const GridDev& G = ctx->density.dev;
+    auto mat3 = [](const float* m, const float* v, float* out) {
+        for (int r = 0; r < 3; ++r) out[r] = std::fmaf(v[0], m[r * 3], std::fmaf(v[1], m[r * 3 + 1], v[2] * m[r * 3 + 2]));
+    };
+    float di[3], q[3];
+    mat3(G.invMat, d, di);
+    const float len = std::sqrt(di[0] * di[0] + di[1] * di[1] + di[2] * di[2]), inv_len = 1.0f / len;
+    const float dir_idx[3] = {inv_len * di[0], inv_len * di[1], inv_len * di[2]};
+    mat3(G.invMat, dir_idx, q);
+    const float scale = 1.0f / std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);
+    auto index_at = [&](float t_world, float* out) { // Ray::eval = origin + direction * t, then worldToIndexF
+        const float w[3] = {o[0] + d[0] * t_world - G.vec[0], o[1] + d[1] * t_world - G.vec[1], o[2] + d[2] * t_world - G.vec[2]};
+        mat3(G.invMat, w, out);
+    };
+    FILE* f = std::fopen(csv_path, "w");
+    if (!f) return fail(ctx, VPTC_ERR_IO, std::string("vptc_trace_pixel_csv: cannot write ") + csv_path);
+    std::fprintf(f, "X0,Y0,Z0,X1,Y1,Z1,T0,T1,Majorant\n");
+    for (uint32_t i = 0; i < n; ++i) {
+        const float t0 = segs[i * 3] * scale, t1 = segs[i * 3 + 1] * scale;
+        float p0[3], p1[3];
+        index_at(t0, p0); index_at(t1, p1);
+        std::fprintf(f, "%.9g,%.9g,%.9g,%.9g,%.9g,%.9g,%.9g,%.9g,%.9g\n", p0[0], p0[1], p0[2], p1[0], p1[1], p1[2], t0, t1, segs[i * 3 + 2]);
+    }
+    std::fclose(f);
     return VPTC_OK;
 }
 
