@@ -7,10 +7,14 @@ from volume_path_tracer_b200 import api, scenes
 variants = [int(v) for v in os.environ.get("VARIANTS", "1,2").split(",")]
 threshes = os.environ.get("THRESH", "").split(";") if os.environ.get("THRESH") else [None]  # "12,8,8,12;16,8,8,16"
 cases = [("fire", 1.0, 16), ("fire_lowscattering", 1.0, 16), ("wdas_cloud", 0.25, 8), ("dense512", 1.0, 8)]
+if os.environ.get("FULL_CLOUD"):  # the full-resolution WDAS-shaped cloud (3.6 GB grid) as an extra case
+    cases.append(("wdas_cloud", 1.0, 8))
 if os.environ.get("WAVES"):  # override the waves per launch of every case
     cases = [(n, f, int(os.environ["WAVES"])) for n, f, _ in cases]
 if os.environ.get("CASES"):
     cases = [c for c in cases if c[0] in os.environ["CASES"].split(",")]
+if os.environ.get("ONLY_FULL_CLOUD"):
+    cases = [("wdas_cloud", 1.0, int(os.environ.get("WAVES", 32)))]
 pools = os.environ.get("POOL", "").split(";") if os.environ.get("POOL") else [None]  # variant 3: "3,20;2,16" = HOT passes, min HOT lanes
 if pools != [None]:
     threshes = pools

@@ -267,9 +267,11 @@ __global__ void __launch_bounds__(POOL_THREADS, VPT_POOL_MIN_BLOCKS) vpt_render_
                         if (mode == M_DRAW && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
                             pend_u = rng.uniform();
                             // conservative SFU prefilter of `t < seg.t1` (see variant 2): clear overshoots are settled here, the rest goes to EVAL
-                            const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
-                            const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
-                            if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
+                            float l2;
+                            asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(1.0f - pend_u));
+                            const float lp = l2 * (-0.69314718f * 0.9999f) - 1.0e-6f;
+                            const float gap = (m.seg_t1 - m.seg_t0) + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f);
+                            if (lp > gap * (m.seg_dmaj * S.sigma_t * m.scale)) { // certainly t >= seg.t1: segment dropped
                                 mode = M_STEP;
                                 if (m.t0 >= m.t1) POOL_RAY_FINISHED();
                                 else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }

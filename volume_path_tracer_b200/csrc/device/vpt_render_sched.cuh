@@ -28,6 +28,9 @@ namespace vptd {
 #ifndef VPT_HOT_REPS
 #define VPT_HOT_REPS 3 // HOT passes per scheduling decision: cuts the ballot/threshold overhead per HDDA step (+4..7 %, profiles/r01_codegen_cliff.txt)
 #endif
+#ifndef VPT_PREFILTER_MUL
+#define VPT_PREFILTER_MUL 1 // overshoot prefilter without the reciprocal: +1 % (profiles/r01_codegen_cliff.txt); 0 = the MUFU.RCP form
+#endif
 #ifndef VPT_SYNC_SETUP
 #define VPT_SYNC_SETUP 0
 #endif
@@ -216,9 +219,19 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 // a conservative test with the SFU approximations (MUFU.LG2 / RCP, error margins far above their
                 // documented bounds) settles the clear cases; everything else — the hits and the ~0.1 % near the
                 // boundary — goes to EVAL, which evaluates t exactly (glibc-exact logf, IEEE divisions) and decides.
+#if VPT_PREFILTER_MUL
+                // the same test multiplied through by k = d_maj * sigma_t * scale > 0 (no reciprocal, no denormal rescaling: 1 - u >= 2^-24):
+                //   0.9999 * (-ln(1 - u)) - 1e-6  >  ((t1 - t0) + margin) * k      (k = 0 / denormal -> true overshoot; k = inf -> EVAL)
+                float l2;
+                asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(1.0f - pend_u));
+                const float lp = l2 * (-0.69314718f * 0.9999f) - 1.0e-6f;
+                const float gap = (m.seg_t1 - m.seg_t0) + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f);
+                if (lp > gap * (m.seg_dmaj * S.sigma_t * m.scale)) { // certainly t >= seg.t1: segment dropped
+#else
                 const float lp = -__logf(1.0f - pend_u) - 1.0e-6f;
                 const float dtp = __fdividef(lp, m.seg_dmaj * S.sigma_t * m.scale) * 0.9999f;
                 if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
+#endif
                     mode = M_STEP;
                     if (m.t0 >= m.t1) VPT_RAY_FINISHED();
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
