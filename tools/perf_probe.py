@@ -22,6 +22,8 @@ for name, factor, waves in cases:
     scene, spec = scenes.load_config(name)
     if factor != 1.0:
         spec = spec.scaled(factor)
+    if os.environ.get("TILE"):  # e.g. TILE=1,1: per-pixel jobs (a configuration the reference accepts: tile_size [1,1])
+        scene.tile_size[0], scene.tile_size[1] = [int(v) for v in os.environ["TILE"].split(",")]
     g = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
     d = torch.zeros((scene.height, scene.width, 4), dtype=torch.float32, device="cuda:0")
     ps = scene.width * scene.height * waves
