@@ -372,6 +372,31 @@ def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
     assert np.allclose(mg, mc, rtol=1e-5, atol=1e-9)
 
 
+@pytest.mark.parametrize("tile", [(1, 1), (2, 2), (4, 4), (3, 5), (16, 2), (96, 54)])
+@pytest.mark.parametrize("name", ["fire", "dense512"])
+def test_tile_sizes_bit_exact(renderer, oracle, loaded, name, tile):
+    """tile_size is a free scene parameter (tile_provider.cpp:95-105): per-pixel jobs (1x1), small tiles (the drain-free
+    settings of DESIGN.md 4.3), non-square ragged tiles and one tile covering the whole frame all reproduce the oracle's
+    per-pixel radiance and draw counts bit for bit, in every kernel variant."""
+    scene0, spec, grids = loaded(name)
+    scene = type(scene0).from_buffer_copy(scene0)
+    scene.tile_size[0], scene.tile_size[1] = tile
+    jids = np.arange(scene.ntiles * scene.num_waves, dtype=np.uint64)
+    xo, no, co = oracle.volume(grids).trace_jobs(scene, jids)
+    film_o = np.zeros((scene.height, scene.width, 4), np.float32)
+    oracle.volume(grids).render(scene, film_o)
+    try:
+        for v in (2, 3):
+            renderer.set_kernel_variant(v)
+            xg, ng = renderer.trace_jobs(scene, jids)
+            assert np.array_equal(ng, no) and np.array_equal(xg, xo)
+            f = renderer.run(scene, renderer.new_film(scene))
+            assert np.array_equal(f[..., 3], film_o[..., 3]) and np.allclose(f, film_o, rtol=1e-5, atol=1e-7)
+    finally:
+        renderer.set_kernel_variant(2)
+    assert (film_o[..., 3] == scene.num_waves).all()
+
+
 @pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
 def test_kernel_variants_agree(renderer, loaded, name):
     """The nested (0), flat (1), stage-scheduled (2) and job-pool (3) megakernels are four schedules of the same
