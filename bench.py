@@ -210,7 +210,7 @@ def run_reference(args):
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -358,7 +358,7 @@ def run_ours(args):
         if not args.no_cpu_baseline and world == 1:
             c = cpu_leg(scene, grids, 1, args.cpu_seconds)
             line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["threads"], "kind": "port", "sample": c["sample"], "note": c["kind_note"]}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -366,7 +366,25 @@ def run_ours(args):
     return 0
 
 
+_RESULT_FD = None
+
+
+def emit(line: dict):
+    """The ONE JSON line of the contract, on the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    # Libraries write to fd 1 behind Python's back (NCCL prints "NCCL version ..." there when the box sets NCCL_DEBUG, and its
+    # INFO log too): keep stdout for the result line alone by pointing fd 1 at stderr for the rest of the run.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
