@@ -31,6 +31,9 @@ namespace vptd {
 #ifndef VPT_PREFILTER_MUL
 #define VPT_PREFILTER_MUL 1 // overshoot prefilter without the reciprocal: +1 % (profiles/r01_codegen_cliff.txt); 0 = the MUFU.RCP form
 #endif
+#ifndef VPT_HOT_SINGLE_FINISH
+#define VPT_HOT_SINGLE_FINISH 1 // HOT's two ray-finished sites only mark the lane; the bookkeeping runs once per pass: +1..3 % (profiles/r01_codegen_cliff.txt)
+#endif
 #ifndef VPT_SYNC_SETUP
 #define VPT_SYNC_SETUP 0
 #endif
@@ -204,12 +207,18 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         // stall: 10 % of all stall samples at `majorant != seg_dmaj`) overlaps the draw, the prefilter and the loop
         // overhead instead of sitting between the step and its use. Same operations per lane in the same order.
         if (run_hot && stage == ST_HOT) {
+#if VPT_HOT_SINGLE_FINISH
+            bool fin = false;
+#define HOT_FINISH() do { fin = true; stage = ST_SETUP; } while (0)
+#else
+#define HOT_FINISH() VPT_RAY_FINISHED()
+#endif
             if (mode == M_PEND) { // RayMajorantIterator::next after the step: volume.cpp:60-70
                 mode = M_STEP;
                 if (m.majorant != m.seg_dmaj) {                 // NaN after a failed step: the segment closes at t1
                     m.seg_t1 = fminf(m.t0, m.t1);               // t0 on a successful step (t0 <= t1), t1 when the step left the ray
                     if (m.seg_dmaj > 0.0f) mode = M_DRAW;
-                    else if (m.t0 >= m.t1) VPT_RAY_FINISHED();         // empty segment dropped, iterator.next() -> nullopt
+                    else if (m.t0 >= m.t1) HOT_FINISH();               // empty segment dropped, iterator.next() -> nullopt
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
                 }
             }
@@ -233,10 +242,14 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
 #endif
                     mode = M_STEP;
-                    if (m.t0 >= m.t1) VPT_RAY_FINISHED();
+                    if (m.t0 >= m.t1) HOT_FINISH();
                     else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
                 } else stage = ST_EVAL;
             }
+#if VPT_HOT_SINGLE_FINISH
+            if (fin) VPT_RAY_FINISHED();
+#endif
+#undef HOT_FINISH
             if (mode == M_STEP && stage == ST_HOT) { // one HDDA step, majorant fetch issued   volume.cpp:53-59
                 if (!hdda_step_bf(m)) m.majorant = __int_as_float(0x7fc00000);
                 else {
