@@ -339,7 +339,7 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, scene, spec, grids, {
                 "parallelism": f"wave-sharded x{world}, volume replicated, 1 NCCL film reduce per step" if world > 1 else "single GPU",
-                "device_volume_mb": None, "synth_s": round(synth_s, 2), "bake_upload_s": round(bake_s, 2)}),
+                "device_volume_mb": round(r.device_volume_bytes() / 1e6, 1), "synth_s": round(synth_s, 2), "bake_upload_s": round(bake_s, 2)}),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 200, "d2h_bytes_per_step": W * H * 16,
                     "note": "vptc_render: scene POD (200 B) in, float4 film out and accumulated on the host; the volume is staged to HBM once, "
                             "like the reference loads its grids once"},

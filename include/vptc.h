@@ -118,6 +118,8 @@ VPTC_API int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t
 
 /* Device time (CUDA events on ctx's stream) of the kernels of the last render call, milliseconds. */
 VPTC_API float vptc_last_render_ms(const vptc_ctx* ctx);
+/* Bytes of HBM the baked volume (density + temperature: cells, lower slots, tiles, apron bricks) occupies; 0 before vptc_set_volume. */
+VPTC_API uint64_t vptc_device_volume_bytes(const vptc_ctx* ctx);
 VPTC_API int   vptc_get_counters(const vptc_ctx* ctx, vptc_counters* out);
 /* Counting costs atomics; off by default. */
 VPTC_API int   vptc_enable_counters(vptc_ctx* ctx, int enabled);

@@ -88,7 +88,7 @@ class VptError(RuntimeError):
 
 
 EXPORTS = [
-    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms",
+    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms", "vptc_device_volume_bytes",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_sample_grid", "vptc_film_to_image",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
@@ -118,6 +118,8 @@ def lib() -> C.CDLL:
     L.vptc_render_device.argtypes = [vp, C.POINTER(Scene), u32, u32, u32, vp]
     L.vptc_last_render_ms.argtypes = [vp]
     L.vptc_last_render_ms.restype = C.c_float
+    L.vptc_device_volume_bytes.argtypes = [vp]
+    L.vptc_device_volume_bytes.restype = C.c_uint64
     L.vptc_get_counters.argtypes = [vp, C.POINTER(Counters)]
     L.vptc_enable_counters.argtypes = [vp, C.c_int]
     L.vptc_set_kernel_variant.argtypes = [vp, C.c_int]
@@ -274,6 +276,9 @@ class Renderer:
         c = Counters()
         _check(lib().vptc_get_counters(self._ctx, C.byref(c)), self._ctx)
         return c
+
+    def device_volume_bytes(self) -> int:
+        return int(lib().vptc_device_volume_bytes(self._ctx))
 
     def last_render_ms(self) -> float:
         return float(lib().vptc_last_render_ms(self._ctx))

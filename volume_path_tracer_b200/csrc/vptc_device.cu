@@ -271,6 +271,7 @@ int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uin
 }
 
 float vptc_last_render_ms(const vptc_ctx* ctx) { return ctx ? ctx->last_ms : 0.0f; }
+uint64_t vptc_device_volume_bytes(const vptc_ctx* ctx) { return ctx && ctx->has_volume ? uint64_t(ctx->density.bytes) + (ctx->has_temperature ? uint64_t(ctx->temperature.bytes) : 0) : 0; }
 
 int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 {
