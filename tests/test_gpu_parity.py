@@ -386,7 +386,7 @@ def test_tile_sizes_bit_exact(renderer, oracle, loaded, name, tile):
     film_o = np.zeros((scene.height, scene.width, 4), np.float32)
     oracle.volume(grids).render(scene, film_o)
     try:
-        for v in (2, 3, 4):
+        for v in (2, 3):
             renderer.set_kernel_variant(v)
             xg, ng = renderer.trace_jobs(scene, jids)
             assert np.array_equal(ng, no) and np.array_equal(xg, xo)
@@ -399,14 +399,14 @@ def test_tile_sizes_bit_exact(renderer, oracle, loaded, name, tile):
 
 @pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
 def test_kernel_variants_agree(renderer, loaded, name):
-    """The nested (0), flat (1), stage-scheduled (2) and job-pool (3: state in shared memory, 4: cold state in global
-    memory) megakernels are five schedules of the same arithmetic: per-job radiance, RNG draw counts and work counters must be bit-identical."""
+    """The nested (0), flat (1), stage-scheduled (2) and job-pool (3) megakernels are four schedules of the same
+    arithmetic: per-job radiance, RNG draw counts and work counters must be bit-identical."""
     scene, spec, grids = loaded(name)
     jids = np.arange(scene.ntiles * scene.num_waves, dtype=np.uint64)
     res = []
     try:
         renderer.enable_counters(True)
-        for v in (0, 1, 2, 3, 4):
+        for v in (0, 1, 2, 3):
             renderer.set_kernel_variant(v)
             x, n = renderer.trace_jobs(scene, jids)
             f = renderer.run(scene, renderer.new_film(scene))

@@ -262,8 +262,7 @@ static void launch_variant(const RenderArgs& args, int variant, int grid_blocks,
     if (variant == 0) vpt_render_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
     else if (variant == 1) vpt_render_flat_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
     else if (variant == 2) vpt_render_sched_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
-    else if (variant == 3) vpt_render_pool_kernel<TRACE, COUNT, false><<<grid_blocks, pool_threads<false>(), pool_smem_bytes<TRACE, COUNT, false>(), stream>>>(args);
-    else vpt_render_pool_kernel<TRACE, COUNT, true><<<grid_blocks, pool_threads<true>(), pool_smem_bytes<TRACE, COUNT, true>(), stream>>>(args);
+    else vpt_render_pool_kernel<TRACE, COUNT><<<grid_blocks, POOL_THREADS, pool_smem_bytes<TRACE, COUNT>(), stream>>>(args);
 }
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream)
 {
@@ -276,20 +275,15 @@ static int occupancy_variant(int variant)
 {
     int n = 0;
     if (variant == 3) { // the pool needs more than the default 48 KB of dynamic shared memory: opt in (idempotent)
-        if (cudaFuncSetAttribute(vpt_render_pool_kernel<TRACE, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pool_smem_bytes<TRACE, COUNT, false>())) != cudaSuccess) return 0;
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_pool_kernel<TRACE, COUNT, false>, pool_threads<false>(), pool_smem_bytes<TRACE, COUNT, false>()) == cudaSuccess ? n : 0;
-    }
-    if (variant == 4) {
-        if (cudaFuncSetAttribute(vpt_render_pool_kernel<TRACE, COUNT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pool_smem_bytes<TRACE, COUNT, true>())) != cudaSuccess) return 0;
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_pool_kernel<TRACE, COUNT, true>, pool_threads<true>(), pool_smem_bytes<TRACE, COUNT, true>()) == cudaSuccess ? n : 0;
+        if (cudaFuncSetAttribute(vpt_render_pool_kernel<TRACE, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pool_smem_bytes<TRACE, COUNT>())) != cudaSuccess) return 0;
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_pool_kernel<TRACE, COUNT>, POOL_THREADS, pool_smem_bytes<TRACE, COUNT>()) == cudaSuccess ? n : 0;
     }
     const cudaError_t e = variant == 0   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
                           : variant == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_flat_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0)
                                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<TRACE, COUNT>, VPT_BLOCK_THREADS, 0);
     return e == cudaSuccess ? n : 0;
 }
-int render_jobs_per_block(int variant) { return variant == 3 ? pool_jobs_per_block<false>() : (variant == 4 ? pool_jobs_per_block<true>() : VPT_BLOCK_THREADS); }
-size_t render_pool_cold_bytes(int variant, int grid_blocks) { return variant == 4 ? size_t(grid_blocks) * pool_jobs_per_block<true>() * POOL_COLD_WORDS * 4 : 0; }
+int render_jobs_per_block(int variant) { return variant == 3 ? POOL_JOBS_PER_BLOCK : VPT_BLOCK_THREADS; }
 int render_blocks_per_sm(int variant, bool trace, bool count)
 {
     if (trace) return count ? occupancy_variant<true, true>(variant) : occupancy_variant<true, false>(variant);

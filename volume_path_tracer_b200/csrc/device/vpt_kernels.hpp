@@ -25,18 +25,15 @@ struct RenderArgs {
     uint32_t* trace_ndraws;
     CountersDev* counters;        // COUNT builds
     int sched_thresh[4];          // variant 2: lanes needed to run SETUP / HOT / - / EVAL in an iteration
-    int pool_params[4];           // variants 3, 4: {HOT passes per scheduling decision, queued slots needed to run HOT, EVAL, SETUP}
-    uint32_t* pool_cold;          // variant 4: 64-byte cold record per job slot, render_pool_cold_bytes(grid_blocks) bytes
+    int pool_params[4];           // variant 3: {HOT passes per scheduling decision, queued slots needed to run HOT, EVAL, SETUP}
 };
 
 cudaError_t upload_cie_table(const float* cie471x3);
 // variant: 0 = nested megakernel (first version), 1 = flat state machine, 2 = flat + warp-level stage scheduling,
-//          3 = per-warp job pool in shared memory (more jobs than lanes, stage queues compacted onto lanes),
-//          4 = 3 with the cold words of a job in L2-resident global memory (30 instead of 20 warps per SM)
+//          3 = per-warp job pool in shared memory (more jobs than lanes, stage queues compacted onto lanes)
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream);
 int render_blocks_per_sm(int variant, bool trace, bool count);
 int render_jobs_per_block(int variant); // jobs a resident block works on at a time (grid sizing)
-size_t render_pool_cold_bytes(int variant, int grid_blocks); // variant 4: size of RenderArgs::pool_cold (0 otherwise)
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
 cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);

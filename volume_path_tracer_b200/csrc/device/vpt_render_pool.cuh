@@ -24,57 +24,40 @@ namespace vptd {
 #define VPT_POOL_SLOTS 64 // job slots per warp (33..64)
 #endif
 #ifndef VPT_POOL_WARPS
-#define VPT_POOL_WARPS 10 // variant 3: warps per block; 10 x 64 slots x 160 B + tables = 107 KB -> 2 blocks per SM (20 warps)
-#endif
-#ifndef VPT_POOL_WARPS_CG
-#define VPT_POOL_WARPS_CG 15 // variant 4 (cold words in global memory, 108 B per job in shared memory): 2 blocks per SM (30 warps)
+#define VPT_POOL_WARPS 10 // warps per block; 10 x 64 slots x 160 B + tables = 107 KB -> 2 blocks per SM
 #endif
 #ifndef VPT_POOL_MIN_BLOCKS
 #define VPT_POOL_MIN_BLOCKS 2
 #endif
-// Variant 4 (CG = true) is variant 3 with the COLD words of a job — path origin / direction / radiance, depth, the tile rectangle
-// and pixel cursor — in a 64-byte record in global memory (L2-resident: 18 MB for the whole grid, ld.cg / st.cg), touched only by
-// SETUP and by EVAL's real collisions; what HOT and EVAL stream (27 words) stays in shared memory. That is what lets 30 instead of
-// 20 warps per SM hold 64 jobs each. "Add the infinite light" at a ray's end becomes a flag bit applied by the next SETUP (same
-// value: nothing else touches L in between), so HOT and EVAL's overshoot path never wait on global memory.
-template <bool CG> __host__ __device__ constexpr int pool_warps() { return CG ? VPT_POOL_WARPS_CG : VPT_POOL_WARPS; }
-template <bool CG> __host__ __device__ constexpr int pool_threads() { return pool_warps<CG>() * 32; }
-template <bool CG> __host__ __device__ constexpr int pool_jobs_per_block() { return pool_warps<CG>() * VPT_POOL_SLOTS; }
-constexpr int POOL_COLD_WORDS = 16; // global record per job slot (variant 4)
+constexpr int POOL_THREADS = VPT_POOL_WARPS * 32;
+constexpr int POOL_JOBS_PER_BLOCK = VPT_POOL_WARPS * VPT_POOL_SLOTS;
 
-// slot words in shared memory. Mutable marching state first (what HOT stores back), then per-ray constants, the shadow ray's
-// transmittance, then (variant 3 only) the cold path state.
+// slot words. Mutable marching state first (what HOT stores back), then per-ray constants, then the cold path state.
 enum : int {
     W_FLAGS = 0, W_RLO, W_RHI, W_T0, W_VX, W_VY, W_VZ, W_NX, W_NY, W_NZ, W_MAJ, W_ST0, W_ST1, W_SDM, W_PENDU,
-    W_EX, W_EY, W_EZ, W_DX, W_DY, W_DZ, W_IX, W_IY, W_IZ, W_SCALE, W_T1, W_TRAY,
-    W_COLD = 27 // variant 3: the cold words K_* follow here; variant 4: they live in the global record
+    W_EX, W_EY, W_EZ, W_DX, W_DY, W_DZ, W_IX, W_IY, W_IZ, W_SCALE, W_T1,
+    W_POS, W_POS1, W_POS2, W_RD, W_RD1, W_RD2, W_L, W_L1, W_L2, W_TRAY, W_DEPTH, W_XY0, W_SXY, W_XY,
+    W_WORDS = 40, W_J = 40, W_DRAWS = 41, W_WORDS_DIAG = 42 // TRACE / COUNT builds carry the job index and the draw count
 };
-enum : int { K_POS = 0, K_RD = 3, K_L = 6, K_DEPTH = 9, K_XY0 = 10, K_SXY = 11, K_XY = 12, K_J = 13 /* TRACE builds */, K_WORDS = 14 };
-// words per slot in shared memory: TRACE / COUNT builds also carry the job's draw count (and variant 3 the job index K_J)
-template <bool CG, bool DIAG> __host__ __device__ constexpr int pool_words() { return CG ? (DIAG ? W_COLD + 1 : W_COLD) : (DIAG ? W_COLD + K_WORDS + 1 : W_COLD + K_XY + 1); }
-// W_FLAGS: bits 0-1 stage, 2-3 sub-phase, 4 shadow, 5 pixel_open, 6-7 marching mode, 8 infinite light pending (variant 4), 10.. HDDA dim
-constexpr uint32_t FL_SHADOW = 16u, FL_PIXEL_OPEN = 32u, FL_INF = 256u;
-constexpr int FL_DIM_SHIFT = 10;
+// W_FLAGS: bits 0-1 stage, 2-3 sub-phase, 4 shadow, 5 pixel_open, 6-7 marching mode, 8.. HDDA dim
+constexpr uint32_t FL_SHADOW = 16u, FL_PIXEL_OPEN = 32u;
 
-template <bool CG> __host__ __device__ constexpr size_t pool_smem_tables() { return 256 /*logf table*/ + 1504 * 4 /*blackbody*/ + 32 /*shadow RayDir*/ + pool_warps<CG>() * 64 /*assign lists*/; }
-template <bool TRACE, bool COUNT, bool CG>
-__host__ __device__ constexpr size_t pool_smem_bytes() { return pool_smem_tables<CG>() + size_t(pool_warps<CG>()) * VPT_POOL_SLOTS * pool_words<CG, TRACE || COUNT>() * 4; }
+constexpr size_t POOL_SMEM_TABLES = 256 /*logf table*/ + 1504 * 4 /*blackbody*/ + 32 /*shadow RayDir*/ + VPT_POOL_WARPS * 64 /*assign lists*/;
+template <bool TRACE, bool COUNT>
+constexpr size_t pool_smem_bytes() { return POOL_SMEM_TABLES + size_t(VPT_POOL_WARPS) * VPT_POOL_SLOTS * ((TRACE || COUNT) ? W_WORDS_DIAG : W_WORDS) * 4; }
 
-template <bool TRACE, bool COUNT, bool CG>
-__global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_render_pool_kernel(const RenderArgs A)
+template <bool TRACE, bool COUNT>
+__global__ void __launch_bounds__(POOL_THREADS, VPT_POOL_MIN_BLOCKS) vpt_render_pool_kernel(const RenderArgs A)
 {
     constexpr int P = VPT_POOL_SLOTS;
-    constexpr int NW = pool_words<CG, TRACE || COUNT>();
-    constexpr int W_DRAWS = NW - 1; // TRACE / COUNT builds only
+    constexpr int NW = (TRACE || COUNT) ? W_WORDS_DIAG : W_WORDS;
     static_assert(P > 32 && P <= 64, "a warp's pool holds 33..64 job slots");
     extern __shared__ __align__(16) unsigned char pool_smem[];
     double* logtab = reinterpret_cast<double*>(pool_smem);
     float* bb = reinterpret_cast<float*>(pool_smem + 256);
     RayDir* shadow_dir_p = reinterpret_cast<RayDir*>(pool_smem + 256 + 1504 * 4);
     uint8_t* assign = pool_smem + 256 + 1504 * 4 + 32 + (threadIdx.x >> 5) * 64;
-    // variant 4: this warp's cold records in global memory, 16 words per job slot
-    uint32_t* const cold_warp = CG ? A.pool_cold + (size_t(blockIdx.x) * pool_warps<CG>() + (threadIdx.x >> 5)) * size_t(P) * POOL_COLD_WORDS : nullptr;
-    uint32_t* pool = reinterpret_cast<uint32_t*>(pool_smem + pool_smem_tables<CG>()) + size_t(threadIdx.x >> 5) * NW * P;
+    uint32_t* pool = reinterpret_cast<uint32_t*>(pool_smem + POOL_SMEM_TABLES) + size_t(threadIdx.x >> 5) * NW * P;
 
     for (int i = threadIdx.x; i < 1504; i += blockDim.x) bb[i] = i < 1500 ? A.bb_table[i] : 0.0f;
     if (threadIdx.x < 32) logtab[threadIdx.x] = c_logf_table[threadIdx.x];
@@ -83,7 +66,6 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
     for (int s = lane; s < P; s += 32) { // every slot starts in SETUP with an exhausted (empty) job: its first SETUP fetches one
         for (int k = 0; k < NW; ++k) pool[k * P + s] = 0u;
         pool[W_FLAGS * P + s] = uint32_t(ST_SETUP) | uint32_t(PH_NEXT_PIXEL) << 2;
-        if (CG) for (int k = 0; k < POOL_COLD_WORDS; ++k) __stcg(cold_warp + size_t(s) * POOL_COLD_WORDS + k, 0u);
     }
     __syncthreads();
 
@@ -103,15 +85,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
 #define PSTI(k, v) (sp[(k) * P] = uint32_t(v))
 #define PLD3(k) mk(PLDF(k), PLDF((k) + 1), PLDF((k) + 2))
 #define PST3(k, v) do { PSTF(k, (v).x); PSTF((k) + 1, (v).y); PSTF((k) + 2, (v).z); } while (0)
-    // cold words: shared memory (variant 3) or this slot's global record through L2 (variant 4)
-#define CLDU(k) (CG ? __ldcg(cg + (k)) : sp[(W_COLD + (k)) * P])
-#define CSTU(k, v) do { if (CG) __stcg(cg + (k), uint32_t(v)); else sp[(W_COLD + (k)) * P] = uint32_t(v); } while (0)
-#define CLDF(k) __uint_as_float(CLDU(k))
-#define CSTF(k, v) CSTU(k, __float_as_uint(v))
-#define CLD3(k) mk(CLDF(k), CLDF((k) + 1), CLDF((k) + 2))
-#define CST3(k, v) do { CSTF(k, (v).x); CSTF((k) + 1, (v).y); CSTF((k) + 2, (v).z); } while (0)
-    // L += infinite light (worker.cpp:198-200): at once (variant 3) or as a flag the next SETUP applies before the film add (variant 4)
-#define PADD_INF_LIGHT() do { if (CG) inf = true; else { CSTF(K_L, CLDF(K_L) + S.inf_light[0]); CSTF(K_L + 1, CLDF(K_L + 1) + S.inf_light[1]); CSTF(K_L + 2, CLDF(K_L + 2) + S.inf_light[2]); } } while (0)
+#define PADD_INF_LIGHT() do { PSTF(W_L, PLDF(W_L) + S.inf_light[0]); PSTF(W_L1, PLDF(W_L1) + S.inf_light[1]); PSTF(W_L2, PLDF(W_L2) + S.inf_light[2]); } while (0)
     // the ray left the volume (iterator.next() -> nullopt): back to SETUP
 #define POOL_RAY_FINISHED()                                            \
     do {                                                               \
@@ -119,8 +93,6 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
         else { PADD_INF_LIGHT(); sub = PH_NEXT_PIXEL; }                \
         stage = ST_SETUP;                                              \
     } while (0)
-#define POOL_FLAGS(stage, sub, shadow, pixel_open, mode, inf, dim) \
-    (uint32_t(stage) | uint32_t(sub) << 2 | ((shadow) ? FL_SHADOW : 0u) | ((pixel_open) ? FL_PIXEL_OPEN : 0u) | uint32_t(mode) << 6 | ((inf) ? FL_INF : 0u) | uint32_t(dim) << FL_DIM_SHIFT)
 
     for (;;) {
         __syncwarp(); // the slots' flags written by the lanes that ran them are visible to the census
@@ -154,10 +126,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
         flip ^= 1u;
         __syncwarp();
         const bool active = lane < best;
-        const int my_slot = active ? int(assign[lane]) : 0;
-        uint32_t* sp = pool + my_slot;
-        uint32_t* cg = CG ? cold_warp + size_t(my_slot) * POOL_COLD_WORDS : nullptr;
-        (void)cg;
+        uint32_t* sp = pool + (active ? int(assign[lane]) : 0);
         if (COUNT && lane == 0) {
             ++sd_iters; ++sd_runs[pick]; sd_lanes[pick] += best;
             sd_wait += n_setup + n_hot + n_eval - best; sd_exit += P - n_setup - n_hot - n_eval;
@@ -169,19 +138,18 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
             if (active) {
                 uint32_t fl = PLD(W_FLAGS);
                 int sub = int(fl >> 2) & 3, stage = ST_SETUP;
-                bool shadow = (fl & FL_SHADOW) != 0, pixel_open = (fl & FL_PIXEL_OPEN) != 0, inf = (fl & FL_INF) != 0;
+                bool shadow = (fl & FL_SHADOW) != 0, pixel_open = (fl & FL_PIXEL_OPEN) != 0;
                 Rng rng; rng.state = uint64_t(PLD(W_RLO)) | uint64_t(PLD(W_RHI)) << 32; rng.draws = (TRACE || COUNT) ? PLD(W_DRAWS) : 0u;
                 V3 rd = mk(0.0f, 0.0f, 1.0f); // direction of the ray to begin (unused by a shadow ray: shadow_dir)
                 unsigned int depth = 0;
                 if (sub == PH_NEXT_PIXEL) {
-                    const uint32_t xy0 = CLDU(K_XY0), sxy = CLDU(K_SXY), xy = CLDU(K_XY);
+                    const uint32_t xy0 = PLD(W_XY0), sxy = PLD(W_SXY), xy = PLD(W_XY);
                     int x0 = int(xy0 & 0xffffu), y0 = int(xy0 >> 16), sx = int(sxy & 0xffffu), sy = int(sxy >> 16), x = int(xy & 0xffffu), y = int(xy >> 16);
                     if (pixel_open) { // film(y,x) += (imaging_ratio * L, 1)   worker.cpp:203-204
-                        V3 L = CLD3(K_L);
-                        if (CG && inf) { L.x = L.x + S.inf_light[0]; L.y = L.y + S.inf_light[1]; L.z = L.z + S.inf_light[2]; }
+                        const V3 L = PLD3(W_L);
                         if (COUNT) ++st.pixel_samples;
                         if (TRACE) {
-                            const size_t slot = size_t(CLDU(K_J)) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
+                            const size_t slot = size_t(PLD(W_J)) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
                             A.trace_xyz[slot * 3 + 0] = L.x; A.trace_xyz[slot * 3 + 1] = L.y; A.trace_xyz[slot * 3 + 2] = L.z;
                             A.trace_ndraws[slot] = rng.draws;
                         } else {
@@ -189,7 +157,6 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                         }
                         pixel_open = false;
                     }
-                    inf = false;
                     for (;;) { // next pixel of the job (row-major, worker.cpp:109-110), next job when exhausted
                         if (++x >= sx) { x = 0; ++y; }
                         if (y >= sy) {
@@ -197,7 +164,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                             const unsigned long long j = atomicAdd(A.queue, 1ULL); // TileProvider::next(): m_job_idx.fetch_add(1)
                             if (j >= A.n_jobs) { stage = ST_EXIT; break; }
                             uint64_t jid;
-                            if (TRACE) { jid = A.trace_jids[j]; CSTU(K_J, uint32_t(j)); }
+                            if (TRACE) { jid = A.trace_jids[j]; PSTI(W_J, uint32_t(j)); }
                             else {
                                 const uint64_t k = j / S.ntiles, tile_k = j - k * S.ntiles;
                                 jid = (uint64_t(A.first_wave - 1) + k * A.wave_stride) * S.ntiles + tile_k;
@@ -206,14 +173,14 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                             const int64_t tx0 = int64_t(tile % uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tile / uint64_t(S.ntx)) * S.th;
                             x0 = int(tx0); y0 = int(ty0);
                             sx = int(min(S.W - tx0, S.tw)); sy = int(min(S.H - ty0, S.th));
-                            CSTU(K_XY0, uint32_t(x0) | uint32_t(y0) << 16); CSTU(K_SXY, uint32_t(sx) | uint32_t(sy) << 16);
+                            PSTI(W_XY0, uint32_t(x0) | uint32_t(y0) << 16); PSTI(W_SXY, uint32_t(sx) | uint32_t(sy) << 16);
                             rng.begin_job(S.seed, jid);
                             x = 0; y = 0;
                         }
                         if (S.single_pixel_enabled && (int64_t(x0 + x) != S.single_pixel_x || int64_t(y0 + y) != S.single_pixel_y)) continue;
                         break;
                     }
-                    CSTU(K_XY, uint32_t(x) | uint32_t(y) << 16);
+                    PSTI(W_XY, uint32_t(x) | uint32_t(y) << 16);
                     if (stage != ST_EXIT) { // camera path start   worker.cpp:121-128, camera.hpp:14-23
                         const float j0 = rng.uniform(), j1 = rng.uniform();
                         const float jm = S.use_jitter ? 0.5f : 0.0f;
@@ -221,10 +188,10 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                         rd = normalized(mk(sum3(S.cam_m[0] * rx, S.cam_m[1] * ry, S.cam_m[2] * 0.0f) + S.cam_t[0],
                                            sum3(S.cam_m[3] * rx, S.cam_m[4] * ry, S.cam_m[5] * 0.0f) + S.cam_t[1],
                                            sum3(S.cam_m[6] * rx, S.cam_m[7] * ry, S.cam_m[8] * 0.0f) + S.cam_t[2]));
-                        CST3(K_RD, rd);
-                        CSTF(K_POS, S.cam_pos[0]); CSTF(K_POS + 1, S.cam_pos[1]); CSTF(K_POS + 2, S.cam_pos[2]);
-                        CSTF(K_L, 0.0f); CSTF(K_L + 1, 0.0f); CSTF(K_L + 2, 0.0f);
-                        CSTU(K_DEPTH, 0);
+                        PST3(W_RD, rd);
+                        PSTF(W_POS, S.cam_pos[0]); PSTF(W_POS1, S.cam_pos[1]); PSTF(W_POS2, S.cam_pos[2]);
+                        PSTF(W_L, 0.0f); PSTF(W_L1, 0.0f); PSTF(W_L2, 0.0f);
+                        PSTI(W_DEPTH, 0);
                         shadow = false; pixel_open = true;
                     }
                 } else if (sub == PH_BEGIN_SHADOW) { // sample_Ld   worker.cpp:59-66
@@ -232,15 +199,15 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                     if (COUNT) ++st.shadow_rays;
                 } else { // PH_AFTER_SHADOW: worker.cpp:88-89 then :175-183
                     const V3 wi = mk(S.dist_wi[0], S.dist_wi[1], S.dist_wi[2]);
-                    rd = CLD3(K_RD);
+                    rd = PLD3(W_RD);
                     const float k = henyey_greenstein(dot3(rd, wi), S.g) * PLDF(W_TRAY);
-                    CSTF(K_L, CLDF(K_L) + k * S.dist_Li[0]); CSTF(K_L + 1, CLDF(K_L + 1) + k * S.dist_Li[1]); CSTF(K_L + 2, CLDF(K_L + 2) + k * S.dist_Li[2]);
+                    PSTF(W_L, PLDF(W_L) + k * S.dist_Li[0]); PSTF(W_L1, PLDF(W_L1) + k * S.dist_Li[1]); PSTF(W_L2, PLDF(W_L2) + k * S.dist_Li[2]);
                     const float u0 = rng.uniform(), u1 = rng.uniform();
                     rd = sample_henyey_greenstein(rd, u0, u1, S.g);
-                    CST3(K_RD, rd);
+                    PST3(W_RD, rd);
                     shadow = false;
-                    depth = CLDU(K_DEPTH) + 2u; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
-                    CSTU(K_DEPTH, depth);
+                    depth = PLD(W_DEPTH) + 2u; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
+                    PSTI(W_DEPTH, depth);
                 }
                 int dim = 8, mode = M_STEP;
                 if (stage != ST_EXIT) {
@@ -252,7 +219,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                         March m;
                         CellCache cc; cc.reset();
                         const RayDir rdir = shadow ? *shadow_dir_p : make_ray_dir(G, rd);
-                        if (flat_begin_ray_dir<COUNT>(m, G, cc, CLD3(K_POS), rdir, ray_done, st)) {
+                        if (flat_begin_ray_dir<COUNT>(m, G, cc, PLD3(W_POS), rdir, ray_done, st)) {
                             if (ray_done) POOL_RAY_FINISHED();
                             else {
                                 stage = ST_HOT; dim = m.dim;
@@ -267,7 +234,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                 }
                 PSTI(W_RLO, uint32_t(rng.state)); PSTI(W_RHI, uint32_t(rng.state >> 32));
                 if (TRACE || COUNT) PSTI(W_DRAWS, rng.draws);
-                PSTI(W_FLAGS, POOL_FLAGS(stage, sub, shadow, pixel_open, mode, inf, dim));
+                PSTI(W_FLAGS, uint32_t(stage) | uint32_t(sub) << 2 | (shadow ? FL_SHADOW : 0u) | (pixel_open ? FL_PIXEL_OPEN : 0u) | uint32_t(mode) << 6 | uint32_t(dim) << 8);
             }
         }
         // ---------------------------------------------------------------- HOT: HDDA steps and free-flight draws (software-pipelined as in variant 2)
@@ -276,14 +243,13 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                 const uint32_t fl = PLD(W_FLAGS);
                 int sub = int(fl >> 2) & 3, stage = ST_HOT, mode = int(fl >> 6) & 3;
                 const bool shadow = (fl & FL_SHADOW) != 0;
-                bool inf = false;
                 Rng rng; rng.state = uint64_t(PLD(W_RLO)) | uint64_t(PLD(W_RHI)) << 32; rng.draws = (TRACE || COUNT) ? PLD(W_DRAWS) : 0u;
                 March m;
                 m.ex = PLDF(W_EX); m.ey = PLDF(W_EY); m.ez = PLDF(W_EZ); m.dx = PLDF(W_DX); m.dy = PLDF(W_DY); m.dz = PLDF(W_DZ);
                 m.ix = PLDF(W_IX); m.iy = PLDF(W_IY); m.iz = PLDF(W_IZ); m.scale = PLDF(W_SCALE); m.t0 = PLDF(W_T0); m.t1 = PLDF(W_T1);
                 m.vx = int(PLD(W_VX)); m.vy = int(PLD(W_VY)); m.vz = int(PLD(W_VZ)); m.nx = PLDF(W_NX); m.ny = PLDF(W_NY); m.nz = PLDF(W_NZ);
                 m.majorant = PLDF(W_MAJ); m.seg_t0 = PLDF(W_ST0); m.seg_t1 = PLDF(W_ST1); m.seg_dmaj = PLDF(W_SDM);
-                m.dim = int(fl >> FL_DIM_SHIFT);
+                m.dim = int(fl >> 8);
                 float pend_u = 0.0f;
                 CellCache cc; cc.reset();
 #pragma unroll 1
@@ -328,7 +294,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                 PSTF(W_MAJ, m.majorant); PSTF(W_ST0, m.seg_t0); PSTF(W_ST1, m.seg_t1); PSTF(W_SDM, m.seg_dmaj); PSTF(W_PENDU, pend_u);
                 PSTI(W_RLO, uint32_t(rng.state)); PSTI(W_RHI, uint32_t(rng.state >> 32));
                 if (TRACE || COUNT) PSTI(W_DRAWS, rng.draws);
-                PSTI(W_FLAGS, POOL_FLAGS(stage, sub, shadow, (fl & FL_PIXEL_OPEN) != 0, mode, inf, m.dim));
+                PSTI(W_FLAGS, uint32_t(stage) | uint32_t(sub) << 2 | (fl & (FL_SHADOW | FL_PIXEL_OPEN)) | uint32_t(mode) << 6 | uint32_t(m.dim) << 8);
             }
         }
         // ---------------------------------------------------------------- EVAL: exact free flight, trilinear density, collision   worker.cpp:68-84,148-188
@@ -337,7 +303,6 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                 const uint32_t fl = PLD(W_FLAGS);
                 int sub = int(fl >> 2) & 3, stage = ST_HOT, mode = int(fl >> 6) & 3;
                 const bool shadow = (fl & FL_SHADOW) != 0;
-                bool inf = false;
                 Rng rng; rng.state = uint64_t(PLD(W_RLO)) | uint64_t(PLD(W_RHI)) << 32; rng.draws = (TRACE || COUNT) ? PLD(W_DRAWS) : 0u;
                 March m;
                 m.ex = PLDF(W_EX); m.ey = PLDF(W_EY); m.ez = PLDF(W_EZ); m.dx = PLDF(W_DX); m.dy = PLDF(W_DY); m.dz = PLDF(W_DZ);
@@ -384,7 +349,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                             const float temp_K = temp_adim * S.temperature_scale + S.temperature_offset;
                             const V3 e = blackbody_xyz(bb, temp_K);
                             const float k = p_a * S.le_scale;
-                            CSTF(K_L, CLDF(K_L) + k * e.x); CSTF(K_L + 1, CLDF(K_L + 1) + k * e.y); CSTF(K_L + 2, CLDF(K_L + 2) + k * e.z);
+                            PSTF(W_L, PLDF(W_L) + k * e.x); PSTF(W_L1, PLDF(W_L1) + k * e.y); PSTF(W_L2, PLDF(W_L2) + k * e.z);
                         }
                         float u = rng.uniform() * (((0.0f + p_n) + p_a) + p_s); // sample_discrete  random.hpp:31-47
                         u -= p_n;
@@ -394,7 +359,7 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                             if (u <= 0.0f) sub = PH_NEXT_PIXEL; // absorption: terminated, no infinite light
                             else {                               // scatter (also the fallback choice)
                                 if (COUNT) ++st.scatter_events;
-                                CST3(K_POS, point);
+                                PST3(W_POS, point);
                                 if (S.dist_light_on) sub = PH_BEGIN_SHADOW;
                                 else { PSTF(W_TRAY, 0.0f); sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
                             }
@@ -404,18 +369,11 @@ __global__ void __launch_bounds__(pool_threads<CG>(), VPT_POOL_MIN_BLOCKS) vpt_r
                 PSTF(W_ST0, m.seg_t0); PSTF(W_SDM, m.seg_dmaj);
                 PSTI(W_RLO, uint32_t(rng.state)); PSTI(W_RHI, uint32_t(rng.state >> 32));
                 if (TRACE || COUNT) PSTI(W_DRAWS, rng.draws);
-                PSTI(W_FLAGS, POOL_FLAGS(stage, sub, shadow, (fl & FL_PIXEL_OPEN) != 0, mode, inf, fl >> FL_DIM_SHIFT));
+                PSTI(W_FLAGS, uint32_t(stage) | uint32_t(sub) << 2 | (fl & (FL_SHADOW | FL_PIXEL_OPEN)) | uint32_t(mode) << 6 | (fl & ~0xffu));
             }
         }
     }
 #undef POOL_RAY_FINISHED
-#undef POOL_FLAGS
-#undef CLDU
-#undef CSTU
-#undef CLDF
-#undef CSTF
-#undef CLD3
-#undef CST3
 #undef PADD_INF_LIGHT
 #undef PLD
 #undef PLDF

@@ -50,7 +50,6 @@ struct vptc_ctx {
     int num_sms = 0;
     // scratch film for the host-buffer path
     float* film = nullptr; size_t film_floats = 0;
-    void* pool_cold = nullptr; size_t pool_cold_bytes = 0; // variant 4: cold records of the job slots
     float* pinned = nullptr; size_t pinned_floats = 0;
 };
 
@@ -116,7 +115,7 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     for (int i = 0; i < 4; ++i) A.pool_params[i] = ctx->pool_params[i];
     for (int i = 0; i < 4; ++i) A.pool_params[i] = std::max(1, A.pool_params[i]);
     // variant 3 packs pixel coordinates into 16-bit halves of its slot words: larger frames / tiles take variant 2
-    const int variant = (ctx->variant >= 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
+    const int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
     int per_sm = render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
@@ -124,14 +123,6 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     const unsigned long long per_block = (unsigned long long)(render_jobs_per_block(variant));
     unsigned long long want = (A.n_jobs + per_block - 1) / per_block;
     int blocks = int(std::min<unsigned long long>(want ? want : 1ULL, (unsigned long long)(ctx->num_sms) * per_sm));
-    if (const size_t need = render_pool_cold_bytes(variant, blocks)) {
-        if (need > ctx->pool_cold_bytes) {
-            cudaFree(ctx->pool_cold); ctx->pool_cold = nullptr; ctx->pool_cold_bytes = 0;
-            CU(cudaMalloc(&ctx->pool_cold, need));
-            ctx->pool_cold_bytes = need;
-        }
-        A.pool_cold = static_cast<uint32_t*>(ctx->pool_cold);
-    }
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     CU(launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
@@ -185,7 +176,7 @@ int vptc_create(vptc_ctx** out, int device)
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
     CU(upload_cie_table(vpt_host::cie_table()));
-    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(4, std::max(0, std::atoi(v)));
+    if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(3, std::max(0, std::atoi(v)));
     if (const char* v = std::getenv("VPT_POOL_PARAMS")) // "HOT passes,HOT slots,EVAL slots,SETUP slots" (tuning aid)
         std::sscanf(v, "%d,%d,%d,%d", &ctx->pool_params[0], &ctx->pool_params[1], &ctx->pool_params[2], &ctx->pool_params[3]);
     if (const char* v = std::getenv("VPT_SCHED_THRESH")) // "setup,dda,sample,eval" lanes (tuning aid)
@@ -199,7 +190,7 @@ void vptc_destroy(vptc_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     ctx->density.release(); ctx->temperature.release();
-    cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film); cudaFree(ctx->pool_cold);
+    cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -291,7 +282,7 @@ int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 int vptc_set_kernel_variant(vptc_ctx* ctx, int variant)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: ctx is null");
-    if (variant < 0 || variant > 4) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat), 2 (flat + stage scheduling), 3 (per-warp job pool) or 4 (job pool, cold state in global memory)");
+    if (variant < 0 || variant > 3) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat), 2 (flat + stage scheduling) or 3 (per-warp job pool)");
     ctx->variant = variant;
     return VPTC_OK;
 }
