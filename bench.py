@@ -189,11 +189,27 @@ def cpu_leg(scene, grids, first_wave: int, target_seconds: float, threads: int |
         if i >= warmup:
             times.append(secs); samples.append(c.pixel_samples); counters = c
     total_s, total_n = sum(times), sum(samples)
-    return {"value": total_n / total_s, "seconds": total_s, "steps": steps, "samples_per_step": samples[0], "threads": threads, "flavor": flavor,
+    return {"_vol": vol, "value": total_n / total_s, "seconds": total_s, "steps": steps, "samples_per_step": samples[0], "threads": threads, "flavor": flavor,
             "stride": stride, "setup_s": setup, "counters": counters.as_dict(),
             "sample": (f"every {stride}th of the {ntiles} tiles of one wave per step" if stride > 1 else f"{nw} full wave(s) per step")
                       + f" ({samples[0]} pixel-samples/step, {steps} step(s), {total_s:.1f} s)",
             "kind_note": "CPU restatement of the reference integrator (oracle/), " + ("on the reference's vendored NanoVDB + pcg-cpp headers (oracle/_ref)" if flavor == "ref" else "self-contained build")}
+
+
+def parity_check(renderer, vol, scene, threads: int):
+    """BASELINE.json's "RMSE vs reference": wave 1 of the frame rendered by the CPU oracle and through the C ABI on the GPU, same RNG
+    streams. One sample per pixel, so the two films must be EQUAL (no add-order slack); reported as counts / RMSE / relMSE / max rel. diff."""
+    import numpy as np
+    cpu = np.zeros((scene.height, scene.width, 4), np.float32)
+    vol.render_sample(scene, cpu, 1, 1, 1, threads)
+    gpu = np.zeros_like(cpu)
+    renderer.run(scene, gpu, first_wave=1, n_waves=1)
+    d = gpu[..., :3].astype(np.float64) - cpu[..., :3].astype(np.float64)
+    ref2 = float((cpu[..., :3].astype(np.float64) ** 2).mean())
+    return {"against": "CPU oracle, wave 1 of the full frame, identical pcg32_fast streams", "pixels": int(scene.width * scene.height),
+            "sample_counts_equal": bool(np.array_equal(cpu[..., 3], gpu[..., 3])), "bit_equal_pixels": float((gpu[..., :3] == cpu[..., :3]).all(axis=-1).mean()),
+            "rmse": float(np.sqrt((d ** 2).mean())), "relMSE": float((d ** 2).mean() / max(ref2, 1e-300)),
+            "max_rel_diff": float((np.abs(d) / np.maximum(np.abs(cpu[..., :3].astype(np.float64)), 1e-12)).max())}
 
 
 def run_reference(args):
@@ -358,6 +374,10 @@ def run_ours(args):
         if not args.no_cpu_baseline and world == 1:
             c = cpu_leg(scene, grids, 1, args.cpu_seconds)
             line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["threads"], "kind": "port", "sample": c["sample"], "note": c["kind_note"]}
+            try:
+                line["parity"] = parity_check(r, c["_vol"], scene, c["threads"])
+            except Exception as e:  # the check must never cost the bench line
+                line["parity"] = {"error": repr(e)}
         emit(line)
     if world > 1:
         dist.barrier()
