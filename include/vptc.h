@@ -137,6 +137,14 @@ VPTC_API int   vptc_set_kernel_variant(vptc_ctx* ctx, int variant);
 VPTC_API int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint64_t* jids, size_t n_jobs,
                              float* per_pixel_xyz, uint32_t* per_pixel_ndraws);
 
+/* Debug front-end = Logger<true> + single_pixel (worker.cpp:15-49,113-119; the reference ships Logger<false>, :102): the event log
+ * of the ONE camera path that job `jid` traces through pixel (px, py) when every other pixel of its tile is skipped before drawing.
+ * 8 floats per event {type, 6 arguments, 0}: 0 new_ray(origin, direction)  1 sampled_point(point, density)  2 null
+ * 3 scatter(origin, new direction)  4 absorbed  (5 scatter_terminated: unreachable).
+ * At most cap_events are stored; *n_events receives the true count. Runs the default kernel (variant 2). */
+VPTC_API int vptc_trace_path_log(vptc_ctx* ctx, const vptc_scene* scene, uint64_t jid, int64_t px, int64_t py,
+                                 float* events, size_t cap_events, size_t* n_events);
+
 /* Parity hook = Volume::log_majorant_trace (volume.cpp:176-192): merged majorant segments
  * {t0, t1, d_maj} (index-space t) of n world-space rays; at most max_segs per ray are stored,
  * n_segs[i] receives the true count. */

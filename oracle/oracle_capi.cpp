@@ -135,6 +135,30 @@ int vpto_trace_jobs(void* ctx, const vptc_scene* scene, const uint64_t* jids, si
     return 0;
 }
 
+// Logger<true> + single_pixel (worker.cpp:15-49,113-119): the event log of the one camera path job `jid` traces through pixel
+// (px, py) when every other pixel of its tile is skipped before drawing. 8 floats per event (see Counters::event).
+int vpto_path_log(void* ctx, const vptc_scene* scene_in, uint64_t jid, int64_t px, int64_t py, float* events, size_t cap_events, size_t* n_events)
+{
+    auto* c = static_cast<Ctx*>(ctx);
+    if (!c || !scene_in || !n_events) return -1;
+    vptc_scene scene = *scene_in;
+    scene.worker_parameters.single_pixel_enabled = 1;
+    scene.worker_parameters.single_pixel_coord[0] = px; scene.worker_parameters.single_pixel_coord[1] = py;
+    Volume<S> vol = make_volume(c, scene.volume_parameters);
+    const TileGrid tg(scene);
+    const Camera camera(scene.camera_parameters, tg.W, tg.H);
+    std::vector<float> log;
+    Counters cnt; cnt.log = &log;
+    Rng<S::Engine> rng(scene.seed);
+    auto density_acc = vol.m_density.getAccessor();
+    auto temp_acc = vol.m_temperature.getAccessor();
+    S::Sampler temp_sampler(temp_acc);
+    run_job<S>(scene, vol, camera, tg, jid, rng, density_acc, vol.m_has_temp ? &temp_sampler : nullptr, nullptr, nullptr, nullptr, &cnt);
+    *n_events = log.size() / 8;
+    if (events) std::memcpy(events, log.data(), std::min(log.size(), cap_events * 8) * sizeof(float));
+    return 0;
+}
+
 int vpto_trace_segments(void* ctx, const float* origins, const float* dirs, size_t n_rays, uint32_t max_segs, float* segs, uint32_t* n_segs)
 {
     auto* c = static_cast<Ctx*>(ctx);

@@ -65,6 +65,7 @@ class Oracle:
         L.vpto_render_sample.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, vp, vp, C.POINTER(C.c_double)]
         L.vpto_trace_jobs.argtypes = [vp, vp, vp, sz, vp, vp, vp]
         L.vpto_trace_segments.argtypes = [vp, vp, vp, sz, C.c_uint32, vp, vp]
+        L.vpto_path_log.argtypes = [vp, vp, C.c_uint64, C.c_int64, C.c_int64, vp, sz, C.POINTER(sz)]
         L.vpto_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
         L.vpto_rng.argtypes = [C.c_uint32, C.c_uint64, sz, C.POINTER(C.c_uint64), vp, vp]
         L.vpto_rng.restype = None
@@ -185,6 +186,14 @@ class OracleVolume:
         if rc != 0:
             raise RuntimeError(f"vpto_trace_jobs failed ({rc})")
         return xyz, nd, c
+
+    def path_log(self, scene, jid: int, px: int, py: int, cap: int = 1 << 16) -> np.ndarray:
+        """Logger<true> + single_pixel (worker.cpp:15-49): events of the path job `jid` traces through (px, py); rows of 8 floats."""
+        ev, n = np.zeros((cap, 8), np.float32), C.c_size_t(0)
+        rc = self.L.vpto_path_log(self.ctx, C.addressof(scene), jid, px, py, _ptr(ev), cap, C.byref(n))
+        if rc != 0:
+            raise RuntimeError(f"vpto_path_log failed ({rc})")
+        return ev[: min(n.value, cap)].copy()
 
     def trace_segments(self, origins, dirs, max_segs: int = 256):
         o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)

@@ -35,6 +35,13 @@ namespace vpto {
 struct Counters {
     uint64_t pixel_samples = 0, density_evals = 0, temperature_evals = 0, majorant_fetches = 0, rng_draws = 0,
              scatter_events = 0, shadow_rays = 0;
+    // Logger<true> of src/worker.cpp:15-49 (the reference ships Logger<false>, :102): when set, every camera-path event is appended as
+    // 8 floats {type, 6 arguments, 0}: 0 new_ray(o, d)  1 sampled_point(point, density)  2 null  3 scatter(o, d)  4 absorbed  5 scatter_terminated
+    std::vector<float>* log = nullptr;
+    void event(float type, float a = 0, float b = 0, float c = 0, float d = 0, float e = 0, float f = 0)
+    {
+        if (log) log->insert(log->end(), {type, a, b, c, d, e, f, 0.0f});
+    }
     void add(const Counters& o)
     {
         pixel_samples += o.pixel_samples; density_evals += o.density_evals; temperature_evals += o.temperature_evals;

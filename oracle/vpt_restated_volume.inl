@@ -161,6 +161,7 @@ V3 trace_pixel(const vptc_worker_parameters& params, const Volume<S>& vol, const
     const float jm = params.use_jitter ? 0.5f : 0.0f;
     V3 ro, rd;
     camera.generate_ray(px, py, j0 * jm, j1 * jm, ro, rd);
+    cnt->event(0, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z); // logger.new_ray(r)   worker.cpp:125
 
     V3 L;
     bool terminated = false;
@@ -171,6 +172,7 @@ V3 trace_pixel(const vptc_worker_parameters& params, const Volume<S>& vol, const
         if (!intersection) break;
         MajorantTransmittanceSampler<S> sampler(*intersection, rng, vol.m_density, density_acc, vp.sigma_a + vp.sigma_s, cnt);
         while (auto props = sampler.next()) {
+            cnt->event(1, props->point.x, props->point.y, props->point.z, props->density); // logger.sampled_point   worker.cpp:146
             float p_a = (vp.sigma_a * props->density) / props->sigma_maj;
             float p_s = (vp.sigma_s * props->density) / props->sigma_maj;
             float p_n = std::max<float>(1.0f - p_a - p_s, 0.0f);
@@ -183,17 +185,20 @@ V3 trace_pixel(const vptc_worker_parameters& params, const Volume<S>& vol, const
             }
             ScatterEvent event = sample_discrete({{ScatterEvent::Null, p_n}, {ScatterEvent::Absorption, p_a}, {ScatterEvent::Scatter, p_s}}, rng.uniform());
             if (event == ScatterEvent::Null) {
+                cnt->event(2); // logger.null()   worker.cpp:166
                 continue;
             } else if (event == ScatterEvent::Scatter) {
-                if (depth++ >= params.max_depth) { terminated = true; break; }
+                if (depth++ >= params.max_depth) { cnt->event(5); terminated = true; break; } // logger.scatter_terminated()   :170
                 ++cnt->scatter_events;
                 L += sample_Ld(params, vol, rng, props->point, rd, density_acc, cnt);
                 float u0 = rng.uniform(), u1 = rng.uniform();
                 V3 new_dir = sample_henyey_greenstein(rd, u0, u1, vp.henyey_greenstein_g);
                 ro = props->point; rd = new_dir;
+                cnt->event(3, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z); // logger.scatter(r)   worker.cpp:181
                 scattered = true;
                 break;
             } else {
+                cnt->event(4); // logger.absorbed()   worker.cpp:185
                 terminated = true;
                 break;
             }

@@ -160,6 +160,13 @@ def test_cli_trace_pixel_writes_the_majorant_trace_csv(api, scenes, oracle, tmp_
     mid = (rows[:, 0:3] + rows[:, 3:6]) / 2
     lo, hi = np.array([0, 0, 0]) - 1.0, np.array([50, 60, 50]) + 1.0
     assert ((mid > lo - 64) & (mid < hi + 64)).all()
+    # log.csv: the path event log of wave 1 through that pixel alone (Logger<true> + single_pixel), equal to the oracle's
+    want = vol.path_log(scene, (py // 8) * (-(-scene.width // 8)) + px // 8, px, py)
+    names = ["new_ray", "sampled_point", "null", "scatter", "absorbed", "scatter_terminated"]
+    got = (tmp_path / "log.csv").read_text().strip().split("\n")
+    assert len(got) == len(want) and [g.split(",")[0] for g in got] == [names[int(e[0])] for e in want]
+    first = [np.float32(v) for v in got[0].split(",")[1:]]
+    assert np.array_equal(np.array(first, np.float32), want[0, 1:7])
     env["VPT_TRACE_PIXEL"] = "0,0"  # a corner pixel misses this small volume
     r = subprocess.run([str(VPT), str(scene_path), str(tmp_path / "o.png")], capture_output=True, text=True, timeout=300, env=env, cwd=tmp_path)
     assert r.returncode == 0, r.stderr

@@ -372,6 +372,27 @@ def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
     assert np.allclose(mg, mc, rtol=1e-5, atol=1e-9)
 
 
+@pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
+def test_path_event_log_bit_exact(renderer, oracle, loaded, name):
+    """vptc_trace_path_log = Logger<true> + single_pixel (worker.cpp:15-49,113-119): the device's event list of one camera path
+    (new_ray / sampled_point / null / scatter / absorbed with their arguments) equals the oracle's, float for float."""
+    scene, spec, grids = loaded(name)
+    vol = oracle.volume(grids)
+    ntx = -(-scene.width // int(scene.tile_size[0]))
+    rs = np.random.default_rng(11)
+    total = 0
+    for _ in range(24):
+        px, py, wave = int(rs.integers(0, scene.width)), int(rs.integers(0, scene.height)), int(rs.integers(1, scene.num_waves + 1))
+        jid = (wave - 1) * scene.ntiles + (py // int(scene.tile_size[1])) * ntx + px // int(scene.tile_size[0])
+        want = vol.path_log(scene, jid, px, py)
+        got = renderer.trace_path_log(scene, jid, px, py)
+        assert got.shape == want.shape and np.array_equal(got, want)
+        total += len(want)
+    assert total > 24  # some paths entered the volume
+    # capacity smaller than the log: the true count is still reported (here through the clipped array length == cap)
+    assert len(renderer.trace_path_log(scene, jid, px, py, cap=1)) == 1
+
+
 @pytest.mark.parametrize("tile", [(1, 1), (2, 2), (4, 4), (3, 5), (16, 2), (96, 54)])
 @pytest.mark.parametrize("name", ["fire", "dense512"])
 def test_tile_sizes_bit_exact(renderer, oracle, loaded, name, tile):

@@ -198,3 +198,28 @@ def test_single_pixel_mode(oracle, small_case):
     xyz, nd, _ = vol.trace_jobs(s, np.array([tile], np.uint64))
     slot = (50 % 8) * 8 + 35 % 8
     assert nd[0, slot] > 0 and (np.delete(nd[0], slot) == 0).all()
+
+
+def test_path_log_own_equals_reference_and_is_consistent(oracle, oracle_ref, small_case):
+    """Logger<true> + single_pixel (worker.cpp:15-49,113-119): both oracle builds emit the same event list; it starts with the
+    camera ray, every sampled point is followed by exactly one of null / scatter / absorbed, and a path ends absorbed or by
+    leaving the volume (no event)."""
+    for name in ("fire", "wdas_cloud"):
+        scene, spec, grids = small_case(name)
+        vo, vr = oracle.volume(grids), oracle_ref.volume(grids)
+        ntx = -(-scene.width // int(scene.tile_size[0]))
+        seen = set()
+        for px, py, wave in [(scene.width // 2, scene.height // 2, 1), (scene.width // 2 + 3, scene.height // 2 - 5, 2), (1, 1, 1)]:
+            tile = (py // int(scene.tile_size[1])) * ntx + px // int(scene.tile_size[0])
+            jid = (wave - 1) * scene.ntiles + tile
+            ev = vo.path_log(scene, jid, px, py)
+            assert np.array_equal(ev, vr.path_log(scene, jid, px, py))
+            t = ev[:, 0].astype(int)
+            assert t[0] == 0 and (t == 0).sum() == 1 and not (t == 5).any()
+            o, d = oracle.camera_rays(scene, [px], [py], [0.0], [0.0])
+            assert np.array_equal(ev[0, 1:4], o[0])  # origin = camera position; the direction carries this job's jitter
+            nxt = t[1:][t[:-1] == 1]
+            assert len(nxt) == (t == 1).sum() and np.isin(nxt, (2, 3, 4)).all()
+            assert (t == 4).sum() <= 1 and ((t == 4).sum() == 0 or t[-1] == 4)
+            seen.update(t.tolist())
+        assert {0, 1, 2}.issubset(seen)

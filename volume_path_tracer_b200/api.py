@@ -89,7 +89,7 @@ class VptError(RuntimeError):
 
 EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms", "vptc_device_volume_bytes",
-    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_sample_grid", "vptc_film_to_image",
+    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
 ]
@@ -126,6 +126,7 @@ def lib() -> C.CDLL:
     L.vptc_trace_jobs.argtypes = [vp, C.POINTER(Scene), vp, sz, vp, vp]
     L.vptc_trace_segments.argtypes = [vp, vp, vp, sz, u32, vp, vp]
     L.vptc_trace_pixel_csv.argtypes = [vp, C.POINTER(Scene), C.c_int64, C.c_int64, C.c_char_p]
+    L.vptc_trace_path_log.argtypes = [vp, C.POINTER(Scene), C.c_uint64, C.c_int64, C.c_int64, vp, sz, C.POINTER(sz)]
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.vptc_film_to_image.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
     L.vptc_scene_from_json_file.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
@@ -311,6 +312,12 @@ class Renderer:
         n = np.zeros(len(o), np.uint32)
         _check(lib().vptc_trace_segments(self._ctx, _ptr(o), _ptr(d), len(o), max_segs, _ptr(segs), _ptr(n)), self._ctx)
         return segs, n
+
+    def trace_path_log(self, scene, jid: int, px: int, py: int, cap: int = 1 << 16) -> np.ndarray:
+        """Logger<true> + single_pixel (worker.cpp:15-49): events of the path job `jid` traces through (px, py); rows of 8 floats."""
+        ev, n = np.zeros((cap, 8), np.float32), C.c_size_t(0)
+        _check(lib().vptc_trace_path_log(self._ctx, C.byref(scene), jid, px, py, _ptr(ev), cap, C.byref(n)), self._ctx)
+        return ev[: min(n.value, cap)].copy()
 
     def trace_pixel_csv(self, scene, px: int, py: int, path):
         """majorant_trace.csv of the pixel-centre camera ray (Volume::log_majorant_trace, volume.cpp:176-192)."""

@@ -26,6 +26,8 @@ struct RenderArgs {
     CountersDev* counters;        // COUNT builds
     int sched_thresh[4];          // variant 2: lanes needed to run SETUP / HOT / - / EVAL in an iteration
     int pool_params[4];           // variant 3: {HOT passes per scheduling decision, queued slots needed to run HOT, EVAL, SETUP}
+    float* trace_events;          // trace mode, optional: Logger<true> event log (worker.cpp:15-49), 8 floats per event
+    unsigned long long* trace_event_count; unsigned long long trace_event_cap;
 };
 
 cudaError_t upload_cie_table(const float* cie471x3);

@@ -81,6 +81,17 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     for (int i = 0; i < C_WORDS; ++i) cold[i][lane_col] = 0u; // sx = sy = x = y = 0: the first SETUP fetches a job
     { CellCache r; r.reset(); CSTI(C_CT, r.x); CSTI(C_CT + 1, r.y); CSTI(C_CT + 2, r.z); cold[C_CT + 3][lane_col] = r.code; }
 
+    // Logger<true> (worker.cpp:15-49), trace launches only: {type, 6 arguments, 0} appended in program order (callers trace ONE job)
+#define VPT_EVENT(type, a, b, c, d, e, f)                                                          \
+    do {                                                                                           \
+        if (TRACE && A.trace_events) {                                                             \
+            const unsigned long long i_ = atomicAdd(A.trace_event_count, 1ULL);                    \
+            if (i_ < A.trace_event_cap) {                                                          \
+                float* e_ = A.trace_events + i_ * 8;                                               \
+                e_[0] = float(type); e_[1] = (a); e_[2] = (b); e_[3] = (c); e_[4] = (d); e_[5] = (e); e_[6] = (f); e_[7] = 0.0f; \
+            }                                                                                      \
+        }                                                                                          \
+    } while (0)
     // the ray left the volume (iterator.next() -> nullopt): back to SETUP
 #define VPT_RAY_FINISHED()                                                                            \
     do {                                                                                              \
@@ -158,6 +169,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                                        sum3(S.cam_m[3] * rx, S.cam_m[4] * ry, S.cam_m[5] * 0.0f) + S.cam_t[1],
                                        sum3(S.cam_m[6] * rx, S.cam_m[7] * ry, S.cam_m[8] * 0.0f) + S.cam_t[2]));
                     CST3(C_RD, rd);
+                    VPT_EVENT(0, S.cam_pos[0], S.cam_pos[1], S.cam_pos[2], rd.x, rd.y, rd.z); // logger.new_ray   worker.cpp:125
                     CSTF(C_POS, S.cam_pos[0]); CSTF(C_POS + 1, S.cam_pos[1]); CSTF(C_POS + 2, S.cam_pos[2]);
                     CSTF(C_L, 0.0f); CSTF(C_L + 1, 0.0f); CSTF(C_L + 2, 0.0f);
                     CSTI(C_DEPTH, 0);
@@ -174,6 +186,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 const float u0 = rng.uniform(), u1 = rng.uniform();
                 rd = sample_henyey_greenstein(rd, u0, u1, S.g);
                 CST3(C_RD, rd);
+                VPT_EVENT(3, CLDF(C_POS), CLDF(C_POS + 1), CLDF(C_POS + 2), rd.x, rd.y, rd.z); // logger.scatter(r)   worker.cpp:181
                 shadow = false;
                 depth = unsigned(CLDI(C_DEPTH)) + 2u; // `depth++` at the scatter (worker.cpp:169) and `++depth` of the bounce loop (:130)
                 CSTI(C_DEPTH, depth);
@@ -292,6 +305,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     CSTF(C_TRAY, T_ray);
                 } else {
                     const V3 point = index_to_world(G, pos_idx);
+                    VPT_EVENT(1, point.x, point.y, point.z, density, 0.0f, 0.0f); // logger.sampled_point   worker.cpp:146
                     const float p_a = (S.sigma_a * density) / sigma_maj;
                     const float p_s = (S.sigma_s * density) / sigma_maj;
                     const float p_n = fmaxf(1.0f - p_a - p_s, 0.0f);
@@ -309,10 +323,11 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     }
                     float u = rng.uniform() * (((0.0f + p_n) + p_a) + p_s); // sample_discrete  random.hpp:31-47
                     u -= p_n;
+                    if (TRACE && !(u > 0.0f)) VPT_EVENT(2, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f); // logger.null()   worker.cpp:166
                     if (u > 0.0f) {
                         u -= p_a;
                         stage = ST_SETUP;
-                        if (u <= 0.0f) sub = PH_NEXT_PIXEL; // absorption: terminated, no infinite light
+                        if (u <= 0.0f) { sub = PH_NEXT_PIXEL; VPT_EVENT(4, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f); } // absorption: terminated, no infinite light (logger.absorbed, :185)
                         else {                               // scatter (also the fallback choice)
                             if (COUNT) ++st.scatter_events;
                             CST3(C_POS, point);
@@ -325,6 +340,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
     }
 #undef VPT_RAY_FINISHED
+#undef VPT_EVENT
 #undef CLDF
 #undef CLDI
 #undef CSTF

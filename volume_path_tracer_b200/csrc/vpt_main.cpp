@@ -12,7 +12,8 @@
 //   VPT_CHECKPOINT=F   keep the float4 film + next wave in F (written whenever the image is, and at the end); when F
 //                      exists and matches the scene the render RESUMES from it — num_waves may have been raised since
 //   VPT_TRACE_PIXEL=x,y  also write ./majorant_trace.csv for that pixel's centre ray (Volume::log_majorant_trace, volume.cpp:176-192:
-//                      the ray_visualizer's CSV for scripts/plot_majorant_trace.py), from the device's own segment iterator
+//                      the ray_visualizer's CSV for scripts/plot_majorant_trace.py), from the device's own segment iterator, and ./log.csv,
+//                      the path event log of worker.cpp's Logger<true> in single_pixel mode (scripts/plot_raytrace.py), for wave 1
 //   SIGINT / SIGTERM   = closing the window: finish the waves in flight, save image (+ checkpoint), exit 0
 //                      (TileProvider::stop_at_next_wave, tile_provider.cpp:107-110; main.cpp:133-143)
 #include <algorithm>
@@ -70,6 +71,24 @@ int main(int argc, char* argv[])
         if (std::sscanf(tp, "%lld,%lld", &tx, &ty) != 2) vptFATAL("VPT_TRACE_PIXEL must be \"x,y\"");
         if (vptc_trace_pixel_csv(ctx, &cfg, tx, ty, "majorant_trace.csv") != VPTC_OK) vptFATAL(vptc_last_error(ctx));
         vptINFO("Wrote majorant_trace.csv for pixel (" << tx << ", " << ty << ")");
+        // Logger<true> + single_pixel (worker.cpp:15-49,113-119): log.csv of the path wave 1 traces through that pixel alone
+        const int64_t ntx = cfg.output_size[0] / cfg.tile_size[0] + (cfg.output_size[0] % cfg.tile_size[0] != 0);
+        const uint64_t jid = uint64_t(ty / cfg.tile_size[1]) * uint64_t(ntx) + uint64_t(tx / cfg.tile_size[0]);
+        std::vector<float> ev(size_t(1) << 20);
+        size_t n_ev = 0;
+        if (vptc_trace_path_log(ctx, &cfg, jid, tx, ty, ev.data(), ev.size() / 8, &n_ev) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+        if (FILE* f = std::fopen("log.csv", "w")) {
+            static const char* names[] = {"new_ray", "sampled_point", "null", "scatter", "absorbed", "scatter_terminated"};
+            for (size_t i = 0; i < std::min(n_ev, ev.size() / 8); ++i) {
+                const float* e = &ev[i * 8];
+                const int t = std::min(5, std::max(0, int(e[0])));
+                if (t == 0 || t == 3) std::fprintf(f, "%s,%.9g,%.9g,%.9g,%.9g,%.9g,%.9g\n", names[t], e[1], e[2], e[3], e[4], e[5], e[6]);
+                else if (t == 1) std::fprintf(f, "%s,%.9g,%.9g,%.9g,%.9g\n", names[t], e[1], e[2], e[3], e[4]);
+                else std::fprintf(f, "%s\n", names[t]);
+            }
+            std::fclose(f);
+            vptINFO("Wrote log.csv (" << n_ev << " path events)");
+        } else vptFATAL("cannot write log.csv");
     }
 
     const int64_t W = cfg.output_size[0], H = cfg.output_size[1];

@@ -324,6 +324,45 @@ int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint64_t* jids
     return rc;
 }
 
+int vptc_trace_path_log(vptc_ctx* ctx, const vptc_scene* scene_in, uint64_t jid, int64_t px, int64_t py, float* events, size_t cap, size_t* n_events)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_path_log: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (int rc = check_scene(ctx, scene_in)) return rc;
+    if (!n_events || (cap && !events)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_path_log: null argument");
+    CU(cudaSetDevice(ctx->device));
+    vptc_scene scene = *scene_in; // single_pixel mode: the other pixels of the tile are skipped BEFORE drawing (worker.cpp:113-119)
+    scene.worker_parameters.single_pixel_enabled = 1;
+    scene.worker_parameters.single_pixel_coord[0] = px; scene.worker_parameters.single_pixel_coord[1] = py;
+    const size_t slots = size_t(scene.tile_size[0]) * size_t(scene.tile_size[1]);
+    uint64_t* d_jid = nullptr; float *d_xyz = nullptr, *d_ev = nullptr; uint32_t* d_nd = nullptr; unsigned long long* d_n = nullptr;
+    auto cleanup = [&]() { cudaFree(d_jid); cudaFree(d_xyz); cudaFree(d_nd); cudaFree(d_ev); cudaFree(d_n); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_jid, 8)) != cudaSuccess || (e = cudaMalloc(&d_xyz, slots * 12)) != cudaSuccess || (e = cudaMalloc(&d_nd, slots * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&d_ev, std::max<size_t>(cap, 1) * 32)) != cudaSuccess || (e = cudaMalloc(&d_n, 8)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_path_log: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_jid, &jid, 8, cudaMemcpyHostToDevice, ctx->stream);
+    cudaMemsetAsync(d_n, 0, 8, ctx->stream);
+    RenderArgs A{};
+    A.n_jobs = 1; A.first_wave = 1; A.wave_stride = 1;
+    A.trace_jids = d_jid; A.trace_xyz = d_xyz; A.trace_ndraws = d_nd;
+    A.trace_events = d_ev; A.trace_event_count = d_n; A.trace_event_cap = cap;
+    const int variant = ctx->variant;
+    ctx->variant = 2; // the event hooks live in the default kernel
+    int rc = run_render(ctx, &scene, A, /*trace=*/true);
+    ctx->variant = variant;
+    if (rc == VPTC_OK) {
+        unsigned long long n = 0;
+        e = cudaMemcpy(&n, d_n, 8, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && cap) e = cudaMemcpy(events, d_ev, size_t(std::min<unsigned long long>(n, cap)) * 32, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_trace_path_log: copy back: ") + cudaGetErrorString(e));
+        *n_events = size_t(n);
+    }
+    cleanup();
+    return rc;
+}
+
 int vptc_trace_segments(vptc_ctx* ctx, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_trace_segments: ctx is null");
