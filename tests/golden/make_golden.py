@@ -80,6 +80,17 @@ def main():
         out[f"{name}_film"] = film
         out[f"{name}_film_counters"] = np.array(list(c.as_dict().values()), np.uint64)
         out[f"{name}_leafmax_sum"] = np.array([vol.leaf_maxima().astype(np.float64).sum()])
+        # ---- Logger<true> + single_pixel path event logs (worker.cpp:15-49,113-119) of a few (job, pixel) pairs ----
+        rs = np.random.default_rng(13)
+        ntx = -(-scene.width // int(scene.tile_size[0]))
+        args, logs = [], []
+        for _ in range(8):
+            px, py, wave = int(rs.integers(0, scene.width)), int(rs.integers(0, scene.height)), int(rs.integers(1, waves + 1))
+            jid = (wave - 1) * scene.ntiles + (py // int(scene.tile_size[1])) * ntx + px // int(scene.tile_size[0])
+            ev = vol.path_log(scene, jid, px, py)
+            args.append((jid, px, py, len(ev))); logs.append(ev)
+        out[f"{name}_pathlog_args"] = np.array(args, np.int64)
+        out[f"{name}_pathlog"] = np.concatenate(logs)
         print(name, spec, "segments/ray", nseg.mean(), "film mean", film[..., :3].mean(), c.as_dict())
     np.savez_compressed(HERE / "vectors.npz", **out)
     print("wrote", HERE / "vectors.npz", (HERE / "vectors.npz").stat().st_size, "bytes")

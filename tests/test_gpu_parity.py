@@ -373,7 +373,7 @@ def test_image_within_monte_carlo_noise(renderer, oracle, loaded, name, waves):
 
 
 @pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
-def test_path_event_log_bit_exact(renderer, oracle, loaded, name):
+def test_path_event_log_bit_exact(renderer, oracle, loaded, gold, name):
     """vptc_trace_path_log = Logger<true> + single_pixel (worker.cpp:15-49,113-119): the device's event list of one camera path
     (new_ray / sampled_point / null / scatter / absorbed with their arguments) equals the oracle's, float for float."""
     scene, spec, grids = loaded(name)
@@ -389,6 +389,10 @@ def test_path_event_log_bit_exact(renderer, oracle, loaded, name):
         assert got.shape == want.shape and np.array_equal(got, want)
         total += len(want)
     assert total > 24  # some paths entered the volume
+    off = 0  # and the committed fixtures minted from the vendored-NanoVDB oracle build
+    for gj, gx, gy, n in gold[f"{name}_pathlog_args"]:
+        assert np.array_equal(renderer.trace_path_log(scene, int(gj), int(gx), int(gy)), gold[f"{name}_pathlog"][off:off + n])
+        off += int(n)
     # capacity smaller than the log: the true count is still reported (here through the clipped array length == cap)
     assert len(renderer.trace_path_log(scene, jid, px, py, cap=1)) == 1
 

@@ -223,3 +223,15 @@ def test_path_log_own_equals_reference_and_is_consistent(oracle, oracle_ref, sma
             assert (t == 4).sum() <= 1 and ((t == 4).sum() == 0 or t[-1] == 4)
             seen.update(t.tolist())
         assert {0, 1, 2}.issubset(seen)
+
+
+@pytest.mark.parametrize("name", ["fire", "fire_lowscattering", "wdas_cloud", "dense512"])
+def test_path_log_golden(oracle, small_case, gold, name):
+    """The self-contained oracle reproduces the path event logs minted from the vendored-NanoVDB build (tests/golden/make_golden.py)."""
+    scene, spec, grids = small_case(name)
+    vol = oracle.volume(grids)
+    off = 0
+    for jid, px, py, n in gold[f"{name}_pathlog_args"]:
+        assert np.array_equal(vol.path_log(scene, int(jid), int(px), int(py)), gold[f"{name}_pathlog"][off:off + n])
+        off += int(n)
+    assert off == len(gold[f"{name}_pathlog"])
