@@ -177,6 +177,66 @@ def test_nvdb_roundtrip_and_grid_contract(api, tmp_path):
         api.VolumeGrids.read_from_file(tmp_path / "junk.nvdb")
 
 
+def test_nvdb_container_variants(api, tmp_path):
+    """The loader takes what nanovdb::io::readGrid takes (NV/io/IO.h:204-320,575-618): ZIP-coded segments (u64 size + zlib stream;
+    the author's real files may be compressed), several grids in ONE segment, and raw dumps of concatenated grid buffers
+    (NV/NanoVDB.h:5861-5865); BLOSC and truncated files are errors, not crashes."""
+    import struct
+    import zlib
+    grids = api.synth_volume("fire", (40, 48, 40), 0.5, 2, None)
+    p = tmp_path / "fire.nvdb"
+    grids.write(p)
+    raw = p.read_bytes()
+    # parse our own file: one segment per grid = FileHeader(16) + FileMetaData(176) + name + grid bytes
+    segs, off = [], 0
+    while off < len(raw):
+        magic, version, count, codec = struct.unpack_from("<QIHH", raw, off)
+        assert count == 1 and codec == 0
+        meta = bytearray(raw[off + 16: off + 16 + 176])
+        grid_size, file_size = struct.unpack_from("<QQ", meta, 0)
+        name_size = struct.unpack_from("<I", meta, 8 * 4 + 8 + 48 + 24 + 24)[0]
+        name = raw[off + 192: off + 192 + name_size]
+        data = raw[off + 192 + name_size: off + 192 + name_size + grid_size]
+        assert file_size == grid_size and len(data) == grid_size
+        segs.append((magic, version, meta, name, data))
+        off += 192 + name_size + grid_size
+    assert [s[3].rstrip(b"\0") for s in segs] == [b"density", b"temperature"]
+
+    def check(path):
+        back = api.VolumeGrids.read_from_file(path)
+        assert bytes(back.density.view()) == bytes(grids.density.view()) and bytes(back.temperature.view()) == bytes(grids.temperature.view())
+
+    # 1. ZIP codec, one segment per grid
+    out = b""
+    for magic, version, meta, name, data in segs:
+        z = zlib.compress(data, 6)
+        m = bytearray(meta); struct.pack_into("<Q", m, 8, len(z) + 8)  # fileSize = bytes on disk
+        out += struct.pack("<QIHH", magic, version, 1, 1) + bytes(m) + name + struct.pack("<Q", len(z)) + z
+    (tmp_path / "zip.nvdb").write_bytes(out)
+    assert len(out) < len(raw)
+    check(tmp_path / "zip.nvdb")
+    # 2. both grids in ONE uncompressed segment: header, all metadata + names, then all buffers
+    magic, version = segs[0][0], segs[0][1]
+    out = struct.pack("<QIHH", magic, version, 2, 0) + b"".join(bytes(m) + n for _, _, m, n, _ in segs) + b"".join(d for *_, d in segs)
+    (tmp_path / "one_segment.nvdb").write_bytes(out)
+    check(tmp_path / "one_segment.nvdb")
+    # 3. raw dump of the grid buffers
+    (tmp_path / "raw.nvdb").write_bytes(segs[1][4] + segs[0][4])  # temperature first: lookup is by name
+    check(tmp_path / "raw.nvdb")
+    # 4. BLOSC (codec 2) is refused with a message; truncation is an error
+    magic, version, meta, name, data = segs[0]
+    (tmp_path / "blosc.nvdb").write_bytes(struct.pack("<QIHH", magic, version, 1, 2) + bytes(meta) + name + data)
+    with pytest.raises(api.VptError) as e:
+        api.VolumeGrids.read_from_file(tmp_path / "blosc.nvdb")
+    assert "BLOSC" in str(e.value)
+    (tmp_path / "cut.nvdb").write_bytes(raw[: len(raw) // 3])
+    with pytest.raises(api.VptError):
+        api.VolumeGrids.read_from_file(tmp_path / "cut.nvdb")
+    (tmp_path / "zipcut.nvdb").write_bytes((tmp_path / "zip.nvdb").read_bytes()[:4000])
+    with pytest.raises(api.VptError):
+        api.VolumeGrids.read_from_file(tmp_path / "zipcut.nvdb")
+
+
 def test_grid_header_fields(api):
     g = api.synth_volume("dense", (32, 32, 32), 0.5, 1, (1.0, 2.0, 3.0))
     b = g.density.view()
