@@ -54,6 +54,46 @@ struct TreeView {
     }
 };
 
+// The buffer comes from the caller across the C ABI: every offset the baker is about to follow is checked first, so a corrupt or
+// hostile grid is an error (VPTC_ERR_BAD_GRID), never an out-of-bounds read. check_grid() has validated the node ARRAYS; this
+// validates the root table and that every child offset lands exactly on an element of the next level's array.
+void validate_tree(const TreeView& tv, size_t bytes)
+{
+    const char* base = reinterpret_cast<const char*>(tv.grid);
+    const char* end = base + std::min<uint64_t>(tv.grid->gridSize, bytes);
+    auto inside = [&](const void* p, uint64_t n) { const char* c = static_cast<const char*>(p); return c >= base && c <= end && n <= uint64_t(end - c); };
+    for (int l = 0; l < 4; ++l)
+        if (tv.tree->nodeOffset[l] % 8 != 0) throw std::runtime_error("bake: misaligned tree node offset");
+    if (!inside(tv.root, sizeof(RootData))) throw std::runtime_error("bake: root node out of range");
+    if (!inside(tv.tiles, uint64_t(tv.root->tableSize) * sizeof(RootTile))) throw std::runtime_error("bake: root table out of range");
+    const uint64_t nUpper = tv.tree->nodeCount[2], nLower = tv.tree->nodeCount[1], nLeaf = tv.tree->nodeCount[0];
+    // the target must be element k < count of the array starting at `first` (element size `size`)
+    auto element = [&](const void* parent, int64_t off, const void* first, uint64_t size, uint64_t count) {
+        if (off > int64_t(1) << 46 || off < -(int64_t(1) << 46)) return false; // keeps the sum below in range
+        const int64_t rel = (reinterpret_cast<const char*>(parent) - reinterpret_cast<const char*>(first)) + off; // parent and first lie inside the buffer
+        return rel >= 0 && uint64_t(rel) % size == 0 && uint64_t(rel) / size < count;
+    };
+    for (uint32_t i = 0; i < tv.root->tableSize; ++i)
+        if (tv.tiles[i].child != 0 && !element(tv.root, tv.tiles[i].child, tv.upper0, sizeof(UpperData), nUpper))
+            throw std::runtime_error("bake: root tile child offset does not address an upper node");
+    for (uint64_t ui = 0; ui < nUpper; ++ui) {
+        const UpperData* u = tv.upper0 + ui;
+        for (uint32_t w = 0; w < 32768 / 64; ++w)
+            for (uint64_t bits = u->childMask[w]; bits; bits &= bits - 1) { // set bits only
+                const uint32_t n = w * 64 + uint32_t(__builtin_ctzll(bits));
+                if (!element(u, u->table[n].child, tv.lower0, sizeof(LowerData), nLower)) throw std::runtime_error("bake: upper-node child offset does not address a lower node");
+            }
+    }
+    for (uint64_t li = 0; li < nLower; ++li) {
+        const LowerData* l = tv.lower0 + li;
+        for (uint32_t w = 0; w < 4096 / 64; ++w)
+            for (uint64_t bits = l->childMask[w]; bits; bits &= bits - 1) {
+                const uint32_t n = w * 64 + uint32_t(__builtin_ctzll(bits));
+                if (!element(l, l->table[n].child, tv.leaf0, sizeof(LeafData), nLeaf)) throw std::runtime_error("bake: lower-node child offset does not address a leaf");
+            }
+    }
+}
+
 template <class F>
 void parallel_for(size_t n, F&& f)
 {
@@ -79,6 +119,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
 {
     if (const char* bad = check_grid(data, bytes)) throw std::runtime_error(bad);
     const TreeView tv(data);
+    validate_tree(tv, bytes);
     const GridData* g = tv.grid;
     const size_t nUpper = tv.tree->nodeCount[2], nLower = tv.tree->nodeCount[1], nLeaf = tv.tree->nodeCount[0];
 
