@@ -389,3 +389,62 @@ def test_baker_rejects_corrupt_grids(built, tmp_path):
         assert r.returncode == 0 and "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, (r.stdout + r.stderr)[-3000:]
         baked, rejected = [int(v) for v in r.stdout.split() if v.isdigit()][-2:]
         assert baked + rejected == iters and rejected > 0
+
+
+def test_host_parsers_survive_mutated_input(api, scenes, tmp_path):
+    """Seeded mutation fuzz of the three host-side readers behind the C ABI — scene JSON, `.nvdb` container, film checkpoint: every
+    input either parses or raises VptError (error code + message); none may crash the process (they run in-process here)."""
+    import random
+    rnd = random.Random(5)
+    base = scenes.config_json("fire")
+    alphabet = '{}[]",:0123456789.-+eE tfnul\\\n\t' + "abcxyz_"
+    outcomes = {"ok": 0, "err": 0}
+
+    def attempt(fn):
+        try:
+            fn(); outcomes["ok"] += 1
+        except api.VptError:
+            outcomes["err"] += 1
+        except UnicodeError:
+            pass
+    for _ in range(3000):
+        t = list(base)
+        for _ in range(rnd.choice([1, 1, 2, 3, 8])):
+            if not t:
+                break
+            pos, op = rnd.randrange(len(t)), rnd.random()
+            if op < 0.35: t[pos] = rnd.choice(alphabet)
+            elif op < 0.65: del t[pos]
+            elif op < 0.9: t.insert(pos, rnd.choice(alphabet))
+            else: t = t[:pos]
+        attempt(lambda: api.scene_from_json("".join(t)))
+    for txt in ["", "{", "[" * 100000, "{" * 100000, '{"a":' * 50000, '"' + "\\" * 99999, "1e999999", '{"seed": 1e400}', base.replace("500", "9" * 400), base + base]:
+        attempt(lambda: api.scene_from_json(txt))
+    assert outcomes["err"] > 2000
+
+    def mutate(raw, header):
+        b = bytearray(raw)
+        for _ in range(rnd.choice([1, 2, 4])):
+            pos = rnd.randrange(0, header) if rnd.random() < 0.75 else rnd.randrange(len(b))
+            if rnd.random() < 0.5:
+                b[pos] = rnd.randrange(256)
+            else:
+                v, w = rnd.choice([0, 1, 0xffff, 0xffffffff, 0x7fffffff, 2**63, 2**64 - 1, len(b), len(b) * 2]), rnd.choice([2, 4, 8])
+                pos = min(pos, len(b) - 8)
+                b[pos:pos + w] = (v & (2 ** (8 * w) - 1)).to_bytes(w, "little")
+        return bytes(b[: rnd.randrange(len(b))] if rnd.random() < 0.1 else b)
+    g = api.synth_volume("fire", (24, 24, 24), 0.5, 2, None)
+    p = tmp_path / "a.nvdb"
+    g.write(p)
+    raw = p.read_bytes()
+    for _ in range(600):
+        (tmp_path / "m.nvdb").write_bytes(mutate(raw, 400))
+        attempt(lambda: api.VolumeGrids.read_from_file(tmp_path / "m.nvdb"))
+    scene, _ = scenes.small_variant("fire", (37, 29), 8, 0.2)
+    film = np.random.default_rng(1).random((29, 37, 4)).astype(np.float32)
+    api.film_save(tmp_path / "a.ckpt", scene, film, 5)
+    raw = (tmp_path / "a.ckpt").read_bytes()
+    for _ in range(600):
+        (tmp_path / "m.ckpt").write_bytes(mutate(raw, 300))
+        attempt(lambda: api.film_load(tmp_path / "m.ckpt", scene))
+    assert outcomes["ok"] > 0
