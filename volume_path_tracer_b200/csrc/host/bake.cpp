@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -128,6 +129,8 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
     std::memcpy(h.mat, g->map.matF, sizeof(h.mat));
     std::memcpy(h.invMat, g->map.invMatF, sizeof(h.invMat));
     std::memcpy(h.vec, g->map.vecF, sizeof(h.vec));
+    for (int i = 0; i < 9; ++i) // a NaN / infinite transform turns every ray time into NaN, and `t0 >= t1` never ends a march on NaN
+        if (!std::isfinite(h.mat[i]) || !std::isfinite(h.invMat[i]) || (i < 3 && !std::isfinite(h.vec[i]))) throw std::runtime_error("bake: the grid's index<->world transform is not finite");
     for (int a = 0; a < 3; ++a) { h.bbox_min[a] = tv.root->bbox[a]; h.bbox_max[a] = tv.root->bbox[3 + a]; }
     for (int a = 0; a < 3; ++a) // keeps every device-side coordinate sum in int32 and the cell caches' INT_MIN sentinel outside the grid
         if (h.bbox_min[a] <= h.bbox_max[a] && (h.bbox_min[a] < -(1 << 30) || h.bbox_max[a] > (1 << 30)))
