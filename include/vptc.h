@@ -164,8 +164,13 @@ VPTC_API int vptc_trace_pixel_csv(vptc_ctx* ctx, const vptc_scene* scene, int64_
 VPTC_API int vptc_sample_grid(vptc_ctx* ctx, int grid, const float* index_xyz, size_t n, float* values,
                               uint32_t* dims, float* majorants);
 
+/* Parity hook for blackbody_radiation_xyz (src/precompute_blackbody.cpp:24-52, src/spectral.cpp:7-20): the DEVICE's lookup — table lerp,
+ * exact hits, T <= 0 -> 0, non-finite -> NaN, and the direct 471-term Planck x CIE integration for T >= 49 900 K — for n temperatures
+ * in kelvin; xyz receives n x {X, Y, Z}. Needs no volume. */
+VPTC_API int vptc_blackbody(vptc_ctx* ctx, const float* temps_k, size_t n, float* xyz);
+
 /* Replaces film_to_image (src/main.cpp:12-24, include/vpt/color.hpp:8-30): XYZ/N -> linear sRGB ->
- * sRGB OETF -> clamp -> *255 -> truncate, on the device. Host film in, host RGB8 out. */
+ * sRGB OETF -> clamp -> *255 -> truncate, on the device, byte-identical to the host code (glibc-exact powf). Host film in, host RGB8 out. */
 VPTC_API int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8);
 
 /* ---- host-side helpers (no GPU needed) ---- */

@@ -45,6 +45,17 @@ def libm_check(stride: int = 1):
     return tuple(int(x) for x in out)
 
 
+def libm_check2(stride: int = 1):
+    """Same for expf on +-[2^-126, 88) and powf(x, 1/2.4f) on (0.0031308, FLT_MAX]. -> (n_expf, mismatches_expf, n_powf, mismatches_powf)."""
+    path = _DIR / "libvpt_libm_check.so"
+    if not path.exists():
+        build(ref=False)
+    L = C.CDLL(str(path))
+    out = (C.c_uint64 * 4)()
+    L.vptm_check2(C.c_uint32(stride), out)
+    return tuple(int(x) for x in out)
+
+
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 

@@ -42,8 +42,26 @@ def test_cli_renders_the_oracle_image(api, scenes, oracle, tmp_path):
     oracle.volume(grids).render(scene, film)
     want = oracle.film_to_image(film)
     diff = np.abs(img.astype(int) - want.astype(int))
-    assert diff.max() <= 1 and (diff == 0).mean() > 0.995  # fp32 add order / powf ulp at an 8-bit threshold
+    assert diff.max() <= 1 and (diff == 0).mean() > 0.995  # several waves: fp32 add order of the film sums at an 8-bit threshold (the resolve itself is byte-exact)
     assert img.max() > 30
+
+
+@pytest.mark.gpu
+def test_cli_one_wave_png_is_byte_identical(api, scenes, oracle, tmp_path):
+    """One wave = one sample per pixel: no add-order slack, so the PNG the CLI writes must equal film_to_image of the oracle's film
+    in every byte (integrator bit-exact + resolve byte-exact)."""
+    from PIL import Image
+    grids = api.synth_volume("fire", (50, 60, 50), 1.0, 1, None)
+    (tmp_path / "volumes").mkdir()
+    grids.write(tmp_path / "volumes" / "fire.nvdb")
+    scene_path = _scene(scenes, tmp_path, "../volumes/fire.nvdb", size=(97, 61), waves=1)
+    out = tmp_path / "one.png"
+    r = subprocess.run([str(VPT), str(scene_path), str(out)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    scene, _ = api.read_configuration(scene_path)
+    film = np.zeros((scene.height, scene.width, 4), np.float32)
+    oracle.volume(grids).render(scene, film)
+    assert np.array_equal(np.asarray(Image.open(out)), oracle.film_to_image(film))
 
 
 def test_cli_errors_are_fatal(api, scenes, tmp_path):

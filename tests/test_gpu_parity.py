@@ -311,12 +311,54 @@ def test_density_only_volume_skips_emission(renderer, oracle, api, loaded):
         renderer.set_volume(grids)
 
 
-def test_film_to_image_device(renderer, oracle, loaded, gold):
-    """XYZ/N -> sRGB8 on the device vs film_to_image (main.cpp:12-24): powf may differ by 1 ulp => |diff| <= 1 level."""
-    film = gold["wdas_cloud_film"].copy()
+def test_film_to_image_device_byte_exact(renderer, oracle, gold):
+    """XYZ/N -> sRGB8 on the device == film_to_image on the host (main.cpp:12-24, color.hpp:8-30), BYTE FOR BYTE: the OETF's
+    powf(x, 1/2.4f) is glibc's scheme on the device (libm_exact.cuh, exhaustively checked against glibc over its whole domain)."""
+    for name in SMALL:
+        film = gold[f"{name}_film"].copy()
+        assert np.array_equal(renderer.film_to_image(film), oracle.film_to_image(film))
+    rs = np.random.default_rng(11)
+    film = np.zeros((256, 256, 4), np.float32)
+    film[..., :3] = (rs.gamma(0.4, 0.5, (256, 256, 3)) * 16).astype(np.float32)
+    film[..., 3] = 16
+    film[0, :, 3] = 0                        # never sampled: 0/0 = NaN -> 0
+    film[1, :, :3] = 0                       # black
+    film[2, :, :3] = 3.0e38                  # overflows to +inf in the matrix product
+    film[3, :, :3] = np.linspace(0.0031308 * 15.9, 0.0031308 * 16.1, 256, dtype=np.float32)[:, None]  # around the OETF's knee
+    film[4, :, :3] = np.linspace(15.99, 16.01, 256, dtype=np.float32)[:, None]                          # around 1.0 (254 / 255)
+    film[5, :, 0] = -1.0                     # out-of-gamut negatives
     got, want = renderer.film_to_image(film), oracle.film_to_image(film)
-    diff = np.abs(got.astype(int) - want.astype(int))
-    assert diff.max() <= 1 and (diff == 0).mean() > 0.999
+    assert np.array_equal(got, want)
+    assert got[4].min() >= 253 and got[0].max() == 0
+
+
+def test_blackbody_device_bit_exact(renderer, oracle, gold):
+    """The DEVICE's blackbody_radiation_xyz (precompute_blackbody.cpp:24-52) == the oracle's, bit for bit: table lerp, exact hits, the pad
+    entry for 49 800 K < T < 49 900 K, T <= 0, non-finite, and the direct 471-term integration (spectral.cpp:7-20) for T >= 49 900 K —
+    glibc-exact expf on the device, lambda^5 from the host's libm."""
+    rs = np.random.default_rng(2)
+    T = np.concatenate([gold["bb_temps"], rs.uniform(1, 49800, 20000), np.arange(-100, 50100, 100), rs.uniform(49900, 2e5, 4000), 10 ** rs.uniform(4.7, 38.4, 4000),
+                        [49800.5, 49899.9, 49899.996, 49900, 49900.004, 6e4, 1e5, 1e6, 3.0e38, np.inf, -np.inf, np.nan, -1, 0, 1e-30, 99.99, 100, 100.01]]).astype(np.float32)
+    got, want = renderer.blackbody(T), oracle.blackbody(T)
+    assert np.array_equal(got, want, equal_nan=True)
+    assert np.isnan(got[np.isinf(T) | np.isnan(T)]).all() and (got[T <= 0] == 0).all()
+    assert (got[(T >= 49900) & (T < 1e6)] > 0).all()
+
+
+def test_emission_through_the_direct_blackbody_branch(renderer, oracle, loaded):
+    """temperature_scale = 2000 lifts the fire's temperatures (0..~50) to 300..100 000 K: collisions take the table, the pad entry and the
+    direct-integration branch inside the render kernel; per-job radiance and draw counts stay bit-equal to the oracle."""
+    scene, spec, grids = loaded("fire")
+    hot = scene.copy()
+    hot.volume_parameters.temperature_scale = 2000.0
+    hot.volume_parameters.le_scale = 1e-13
+    jids = np.arange(0, scene.ntiles * 2, 3, dtype=np.uint64)
+    xo, no, co = oracle.volume(grids).trace_jobs(hot, jids)
+    xg, ng = renderer.trace_jobs(hot, jids)
+    assert co.temperature_evals > 0
+    assert np.array_equal(no, ng) and np.array_equal(xo, xg)
+    cold_x, _, _ = oracle.volume(grids).trace_jobs(scene, jids)
+    assert not np.array_equal(cold_x, xo), "the hot scene must actually change the emission"
 
 
 def test_errors(renderer, api, scenes):

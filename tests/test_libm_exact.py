@@ -11,3 +11,13 @@ def test_libm_exact_matches_glibc(built):
     n_log, bad_log, n_sc, bad_sc = oracle_lib.libm_check(stride)
     assert n_log > 1e7 and n_sc > 1e7
     assert bad_log == 0 and bad_sc == 0
+
+
+def test_expf_powf_exact_match_glibc(built):
+    """expf (planck_law, spectral.cpp:16) and powf(x, 1/2.4f) (linsrgb_to_srgb, color.hpp:22) of libm_exact.cuh against this machine's
+    glibc: exhaustive (2.2e9 + 1.1e9 values) with VPT_LIBM_EXHAUSTIVE=1, else every 61st float. Zero mismatches on glibc 2.39 / FMA CPUs."""
+    from oracle import oracle_lib
+    stride = 1 if os.environ.get("VPT_LIBM_EXHAUSTIVE") == "1" else 61
+    n_exp, bad_exp, n_pow, bad_pow = oracle_lib.libm_check2(stride)
+    assert n_exp > 1e7 and n_pow > 1e7
+    assert bad_exp == 0 and bad_pow == 0

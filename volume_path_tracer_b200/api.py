@@ -89,7 +89,7 @@ class VptError(RuntimeError):
 
 EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms", "vptc_device_volume_bytes",
-    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image",
+    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
 ]
@@ -129,6 +129,7 @@ def lib() -> C.CDLL:
     L.vptc_trace_path_log.argtypes = [vp, C.POINTER(Scene), C.c_uint64, C.c_int64, C.c_int64, vp, sz, C.POINTER(sz)]
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.vptc_film_to_image.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
+    L.vptc_blackbody.argtypes = [vp, vp, sz, vp]
     L.vptc_scene_from_json_file.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
     L.vptc_scene_from_json.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
     L.vptc_nvdb_read_grid.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp), C.POINTER(sz)]
@@ -328,6 +329,13 @@ class Renderer:
         v, dm, mj = np.zeros(len(p), np.float32), np.zeros(len(p), np.uint32), np.zeros(len(p), np.float32)
         _check(lib().vptc_sample_grid(self._ctx, grid, _ptr(p), len(p), _ptr(v), _ptr(dm), _ptr(mj)), self._ctx)
         return v, dm, mj
+
+    def blackbody(self, temps_k) -> np.ndarray:
+        """The device's blackbody_radiation_xyz (precompute_blackbody.cpp:24-52) for temperatures in kelvin -> (n, 3) XYZ."""
+        t = np.ascontiguousarray(temps_k, dtype=np.float32).reshape(-1)
+        out = np.zeros((len(t), 3), np.float32)
+        _check(lib().vptc_blackbody(self._ctx, _ptr(t), len(t), _ptr(out)), self._ctx)
+        return out
 
     def film_to_image(self, film: np.ndarray) -> np.ndarray:
         film = np.ascontiguousarray(film, dtype=np.float32)

@@ -13,6 +13,7 @@
 // sinf/cosf argument phi = 2*pi*u in [0, 2*pi) (random.hpp:68-71). Outside [0, 120) / subnormals the routines
 // below are NOT valid and the callers never get there.
 #pragma once
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 
@@ -114,6 +115,112 @@ VPT_HD void sincosf_exact(float y, float& s_out, float& c_out)
     const bool odd = (n & 1) != 0, tiny = abstop12(y) < abstop12(0x1p-12f);
     s_out = tiny ? y : (odd ? cp : sp);
     c_out = tiny ? 1.0f : (odd ? sp : cp);
+}
+
+// ---------------------------------------------------------------- expf / powf (glibc e_expf.c, e_powf.c: the same ARM "optimized routines")
+// Needed where the reference calls them on the HOST side of the hot path and the device must produce the same bytes:
+//   * powf(x, 1/2.4f) in linsrgb_to_srgb (include/vpt/color.hpp:18-30) -> vpt_resolve_kernel (film_to_image on the device);
+//   * expf in planck_law (src/spectral.cpp:16) for the direct 471-term blackbody integration at T >= 49 900 K
+//     (src/precompute_blackbody.cpp:34-36), reachable from the render kernel through temperature_scale.
+// Tables: glibc 2.39's __exp2f_data.tab (2^(i/32) bit patterns minus i<<47) and __powf_log2_data.tab ({1/c, log2 c} x 16), read out of
+// this image's libm.so.6 (tools/extract_libm_tables.py prints them). On x86-64 glibc dispatches these routines to builds compiled with
+// -mfma (sysdeps/x86_64/fpu/multiarch/e_expf-fma.c, e_powf-fma.c) on every CPU that has FMA — the GPU box's host included — so the
+// double-precision a*b+c steps below are fused exactly where that build fuses them. Which steps those are was settled empirically, by
+// exhaustive comparison with this machine's glibc (oracle/libm_check.cpp): expf with every step fused, INCLUDING kd = fma(InvLn2N, x, Shift)
+// and r = fma(InvLn2N, x, -kd): 0 mismatches over every float in [2^-126, 88) (1 mismatch if kd is not fused); powf(x, 1/2.4f) with the
+// polynomial steps fused and y*log2(x) NOT fused into the shift: 0 mismatches over every float in (0.0031308, FLT_MAX] (8 if it is fused).
+#define VPT_EXP2F_TABLE_INIT                                                                                          \
+    {                                                                                                                 \
+        0x3ff0000000000000ULL, 0x3fefd9b0d3158574ULL, 0x3fefb5586cf9890fULL, 0x3fef9301d0125b51ULL,                    \
+        0x3fef72b83c7d517bULL, 0x3fef54873168b9aaULL, 0x3fef387a6e756238ULL, 0x3fef1e9df51fdee1ULL,                    \
+        0x3fef06fe0a31b715ULL, 0x3feef1a7373aa9cbULL, 0x3feedea64c123422ULL, 0x3feece086061892dULL,                    \
+        0x3feebfdad5362a27ULL, 0x3feeb42b569d4f82ULL, 0x3feeab07dd485429ULL, 0x3feea47eb03a5585ULL,                    \
+        0x3feea09e667f3bcdULL, 0x3fee9f75e8ec5f74ULL, 0x3feea11473eb0187ULL, 0x3feea589994cce13ULL,                    \
+        0x3feeace5422aa0dbULL, 0x3feeb737b0cdc5e5ULL, 0x3feec49182a3f090ULL, 0x3feed503b23e255dULL,                    \
+        0x3feee89f995ad3adULL, 0x3feeff76f2fb5e47ULL, 0x3fef199bdd85529cULL, 0x3fef3720dcef9069ULL,                    \
+        0x3fef5818dcfba487ULL, 0x3fef7c97337b9b5fULL, 0x3fefa4afa2a490daULL, 0x3fefd0765b6e4540ULL                     \
+    }
+#define VPT_POWF_LOG2_TABLE_INIT                                                                                      \
+    {                                                                                                                 \
+        0x1.661ec79f8f3bep+0, -0x1.efec65b963019p-2, 0x1.571ed4aaf883dp+0, -0x1.b0b6832d4fca4p-2,                      \
+        0x1.49539f0f010b0p+0, -0x1.7418b0a1fb77bp-2, 0x1.3c995b0b80385p+0, -0x1.39de91a6dcf7bp-2,                      \
+        0x1.30d190c8864a5p+0, -0x1.01d9bf3f2b631p-2, 0x1.25e227b0b8ea0p+0, -0x1.97c1d1b3b7af0p-3,                      \
+        0x1.1bb4a4a1a343fp+0, -0x1.2f9e393af3c9fp-3, 0x1.12358f08ae5bap+0, -0x1.960cbbf788d5cp-4,                      \
+        0x1.0953f419900a7p+0, -0x1.a6f9db6475fcep-5, 0x1.0000000000000p+0, 0x0.0p+0,                                   \
+        0x1.e608cfd9a47acp-1, 0x1.338ca9f24f53dp-4, 0x1.ca4b31f026aa0p-1, 0x1.476a9543891bap-3,                        \
+        0x1.b2036576afce6p-1, 0x1.e840b4ac4e4d2p-3, 0x1.9c2d163a1aa2dp-1, 0x1.40645f0c6651cp-2,                        \
+        0x1.886e6037841edp-1, 0x1.88e9c2c1b9ff8p-2, 0x1.767dcf5534862p-1, 0x1.ce0a44eb17bccp-2                         \
+    }
+
+VPT_HD uint64_t as_u64(double d)
+{
+#if defined(__CUDA_ARCH__)
+    return (uint64_t)__double_as_longlong(d);
+#else
+    uint64_t u; std::memcpy(&u, &d, 8); return u;
+#endif
+}
+VPT_HD double as_f64(uint64_t u)
+{
+#if defined(__CUDA_ARCH__)
+    return __longlong_as_double((long long)u);
+#else
+    double d; std::memcpy(&d, &u, 8); return d;
+#endif
+}
+
+// expf(x) for finite |x| < 88 (no overflow / underflow handling: callers stay inside). `tab` = VPT_EXP2F_TABLE_INIT.
+VPT_HD float expf_exact(float x, const uint64_t* tab)
+{
+    const double xd = double(x);
+    const double InvLn2N = 0x1.71547652b82fep+5, Shift = 0x1.8p+52; // N = 32
+    double kd = fma(InvLn2N, xd, Shift);
+    const uint64_t ki = as_u64(kd);
+    kd -= Shift;
+    const double r = fma(InvLn2N, xd, -kd);
+    uint64_t t = tab[ki & 31u];
+    t += ki << 47;
+    const double s = as_f64(t);
+    const double z = fma(0x1.c6af84b912394p-20, r, 0x1.ebfce50fac4f3p-13); // poly_scaled
+    const double r2 = r * r;
+    double y = fma(0x1.62e42ff0c52d6p-6, r, 1.0);
+    y = fma(z, r2, y);
+    return float(y * s);
+}
+
+// powf(x, y) for positive NORMAL finite x and |y * log2(x)| < 126 (no special cases). `e2` = VPT_EXP2F_TABLE_INIT, `l2` = VPT_POWF_LOG2_TABLE_INIT.
+VPT_HD float powf_exact(float x, float yf, const uint64_t* e2, const double* l2)
+{
+    const uint32_t ix = as_u32(x);
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = int((tmp >> 19) & 15u);
+    const uint32_t top = tmp & 0xff800000u;
+    const int k = int32_t(top) >> 23;
+    const double invc = l2[2 * i], logc = l2[2 * i + 1];
+    const double z = double(as_f32(ix - top));
+    const double r = fma(z, invc, -1.0);
+    const double y0 = logc + double(k);
+    const double r2 = r * r;
+    double y = fma(0x1.27616c9496e0bp-2, r, -0x1.71969a075c67ap-2);
+    const double p = fma(0x1.ec70a6ca7baddp-2, r, -0x1.7154748bef6c8p-1);
+    const double r4 = r2 * r2;
+    double q = fma(0x1.71547652ab82bp0, r, y0);
+    q = fma(p, r2, q);
+    y = fma(y, r4, q); // log2(x)
+    const double xd = double(yf) * y;
+    const double Shift = 0x1.8p+47; // 0x1.8p52 / 32
+    double kd = xd + Shift;
+    const uint64_t ki = as_u64(kd);
+    kd -= Shift;
+    const double rr = xd - kd;
+    uint64_t t = e2[ki & 31u];
+    t += ki << 47;
+    const double s = as_f64(t);
+    const double zz = fma(0x1.c6af84b912394p-5, rr, 0x1.ebfce50fac4f3p-3);
+    const double rr2 = rr * rr;
+    double v = fma(0x1.62e42ff0c52d6p-1, rr, 1.0);
+    v = fma(zz, rr2, v);
+    return float(v * s);
 }
 
 } // namespace vptm

@@ -14,10 +14,15 @@
 namespace vptd {
 
 __constant__ float c_cie[471 * 3];
+__constant__ float c_lambda5[471];                                   // float(pow(double(lambda_m), 5)) per wavelength, from the HOST's libm (spectral.cpp:15)
 __constant__ double c_logf_table[32] = VPT_LOGF_TABLE_INIT;
+__constant__ unsigned long long c_exp2f_table[32] = VPT_EXP2F_TABLE_INIT;   // glibc __exp2f_data.tab (libm_exact.cuh)
+__constant__ double c_powf_log2_table[32] = VPT_POWF_LOG2_TABLE_INIT;       // glibc __powf_log2_data.tab
 
 // ---------------------------------------------------------------- blackbody  src/precompute_blackbody.cpp:24-52
-__device__ __noinline__ V3 spectrum_to_xyz_direct(float T) // T >= 49900 K: direct 471-term integration (spectral.hpp:62-75)
+// Bit-exact with the host: lambda^5 is the host libm's own value per wavelength (471 of them, uploaded at vptc_create), expf is glibc's
+// scheme (libm_exact.cuh, exhaustively checked), everything else is single IEEE fp32 operations in the reference's order.
+__device__ __noinline__ V3 spectrum_to_xyz_direct(float T) // T >= 49900 K: direct 471-term integration (spectral.hpp:62-75, spectral.cpp:7-20)
 {
     float acc[3];
     for (int ch = 0; ch < 3; ++ch) {
@@ -26,10 +31,10 @@ __device__ __noinline__ V3 spectrum_to_xyz_direct(float T) // T >= 49900 K: dire
             const float lambda_m = float(360 + i) * 1e-9f;
             const float c = 299792458.f, h = 6.62606957e-34f, kb = 1.3806488e-23f;
             const float num = 2 * h * c * c;
-            const float lambda5 = float(pow(double(lambda_m), 5.0));
-            const float e = expf((h * c) / (lambda_m * kb * T));
-            const float planck = T <= 0.0f ? 0.0f : num / (lambda5 * (e - 1));
-            integral += c_cie[i * 3 + ch] * planck;
+            const float lambda5 = c_lambda5[i];
+            const float e = vptm::expf_exact((h * c) / (lambda_m * kb * T), reinterpret_cast<const uint64_t*>(c_exp2f_table)); // argument in (0, 0.81] for T >= 49900
+            const float den = lambda5 * (e - 1);
+            integral += c_cie[i * 3 + ch] * (num / den);
         }
         acc[ch] = integral;
     }
@@ -237,6 +242,8 @@ __global__ void vpt_sample_kernel(GridDev G, const float* xyz, size_t n, float* 
 }
 
 // ---------------------------------------------------------------- film_to_image  src/main.cpp:12-24, color.hpp:8-30
+// Byte-exact with the host: the sRGB OETF's powf(x, 1/2.4f) is glibc's scheme (libm_exact.cuh: zero mismatches over every float of
+// (0.0031308, FLT_MAX]); +inf stays +inf (clamps to 255), NaN (a w = 0 pixel: 0/0) has an undefined cast in the reference and is written as 0.
 __global__ void vpt_resolve_kernel(const float4* film, size_t n, uint8_t* rgb)
 {
     const size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
@@ -247,14 +254,32 @@ __global__ void vpt_resolve_kernel(const float4* film, size_t n, uint8_t* rgb)
                           sum3(0.055648f * X, -0.204043f * Y, 1.057311f * Z)};
     for (int c = 0; c < 3; ++c) {
         const float x = lin[c];
-        float s = x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.0f / 2.4f) - 0.055f;
-        s = fminf(fmaxf(s, 0.0f), 1.0f) * 255.0f; // NaN (w = 0) -> fmaxf gives 0
+        float s;
+        if (x <= 0.0031308f) s = 12.92f * x;
+        else {
+            const float p = x <= FLT_MAX ? vptm::powf_exact(x, 1.0f / 2.4f, reinterpret_cast<const uint64_t*>(c_exp2f_table), c_powf_log2_table) : x; // inf, NaN pass through
+            s = 1.055f * p - 0.055f;
+        }
+        s = fminf(fmaxf(s, 0.0f), 1.0f) * 255.0f; // NaN -> fmaxf gives 0
         rgb[i * 3 + c] = (unsigned char)(s);
     }
 }
 
+// Parity hook: the device's blackbody_radiation_xyz (table in global memory here; the render kernels keep it in shared memory).
+__global__ void vpt_blackbody_kernel(const float* __restrict__ bb, const float* temps, size_t n, float* xyz)
+{
+    const size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    const V3 v = blackbody_xyz(bb, temps[i]);
+    xyz[3 * i] = v.x; xyz[3 * i + 1] = v.y; xyz[3 * i + 2] = v.z;
+}
+
 // ---------------------------------------------------------------- launchers
-cudaError_t upload_cie_table(const float* cie471x3) { return cudaMemcpyToSymbol(c_cie, cie471x3, sizeof(float) * 471 * 3); }
+cudaError_t upload_cie_table(const float* cie471x3, const float* lambda5_471)
+{
+    const cudaError_t e = cudaMemcpyToSymbol(c_cie, cie471x3, sizeof(float) * 471 * 3);
+    return e != cudaSuccess ? e : cudaMemcpyToSymbol(c_lambda5, lambda5_471, sizeof(float) * 471);
+}
 
 template <bool TRACE, bool COUNT>
 static void launch_variant(const RenderArgs& args, int variant, int grid_blocks, cudaStream_t stream)
@@ -299,6 +324,12 @@ cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* v
 {
     if (n == 0) return cudaSuccess;
     vpt_sample_kernel<<<unsigned((n + 127) / 128), 128, 0, s>>>(G, xyz, n, values, dims, majorants);
+    return cudaGetLastError();
+}
+cudaError_t launch_blackbody(const float* bb_table, const float* temps, size_t n, float* xyz, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    vpt_blackbody_kernel<<<unsigned((n + 127) / 128), 128, 0, s>>>(bb_table, temps, n, xyz);
     return cudaGetLastError();
 }
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s)

@@ -30,7 +30,7 @@ struct RenderArgs {
     unsigned long long* trace_event_count; unsigned long long trace_event_cap;
 };
 
-cudaError_t upload_cie_table(const float* cie471x3);
+cudaError_t upload_cie_table(const float* cie471x3, const float* lambda5_471); // CIE observer + the host libm's lambda^5 per wavelength
 // variant: 0 = nested megakernel (first version), 1 = flat state machine, 2 = flat + warp-level stage scheduling,
 //          3 = per-warp job pool in shared memory (more jobs than lanes, stage queues compacted onto lanes)
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream);
@@ -38,6 +38,7 @@ int render_blocks_per_sm(int variant, bool trace, bool count);
 int render_jobs_per_block(int variant); // jobs a resident block works on at a time (grid sizing)
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
 cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);
+cudaError_t launch_blackbody(const float* bb_table, const float* temps, size_t n, float* xyz, cudaStream_t s);
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);
 
 } // namespace vptd

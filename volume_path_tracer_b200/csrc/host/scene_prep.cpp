@@ -23,6 +23,11 @@ const float kCIE[471][3] = {
 } // namespace
 
 const float* cie_table() { return &kCIE[0][0]; }
+void lambda5_table(float out[471])
+{
+    // planck_law's `float lambda5 = std::pow(lambda_m, 5)` (spectral.cpp:15): the (float, int) overload evaluates in double
+    for (unsigned int k = 0; k < 471; ++k) out[k] = float(std::pow(static_cast<float>(360 + k) * 1e-9f, 5));
+}
 
 void prepare_scene(const vptc_scene& s, bool has_temperature, vptd::SceneDev& d)
 {

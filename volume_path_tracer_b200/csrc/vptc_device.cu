@@ -169,13 +169,16 @@ int vptc_create(vptc_ctx** out, int device)
     CU(cudaStreamCreate(&ctx->stream)); // blocking stream: ordered after work on the legacy default stream (torch)
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
-    CU(cudaMalloc(&ctx->bb_table, 1500 * sizeof(float)));
+    CU(cudaMalloc(&ctx->bb_table, 1504 * sizeof(float))); // +1 zero entry: the reference reads bb_xyz[500] for 49 800 K < T < 49 900 K
+    CU(cudaMemset(ctx->bb_table, 0, 1504 * sizeof(float)));
     CU(cudaMalloc(&ctx->queue, sizeof(unsigned long long)));
     CU(cudaMalloc(&ctx->counters, sizeof(CountersDev)));
     std::vector<float> bb(1500);
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
-    CU(upload_cie_table(vpt_host::cie_table()));
+    float lambda5[471];
+    vpt_host::lambda5_table(lambda5);
+    CU(upload_cie_table(vpt_host::cie_table(), lambda5));
     if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(3, std::max(0, std::atoi(v)));
     if (const char* v = std::getenv("VPT_POOL_PARAMS")) // "HOT passes,HOT slots,EVAL slots,SETUP slots" (tuning aid)
         std::sscanf(v, "%d,%d,%d,%d", &ctx->pool_params[0], &ctx->pool_params[1], &ctx->pool_params[2], &ctx->pool_params[3]);
@@ -462,6 +465,27 @@ int vptc_sample_grid(vptc_ctx* ctx, int grid, const float* xyz, size_t n, float*
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cleanup();
     if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_sample_grid: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+int vptc_blackbody(vptc_ctx* ctx, const float* temps_k, size_t n, float* xyz)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_blackbody: ctx is null");
+    if (n == 0) return VPTC_OK;
+    if (!temps_k || !xyz) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_blackbody: null argument");
+    CU(cudaSetDevice(ctx->device));
+    float *d_t = nullptr, *d_o = nullptr;
+    auto cleanup = [&]() { cudaFree(d_t); cudaFree(d_o); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_t, n * 4)) != cudaSuccess || (e = cudaMalloc(&d_o, n * 12)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_blackbody: cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    e = cudaMemcpyAsync(d_t, temps_k, n * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_blackbody(ctx->bb_table, d_t, n, d_o, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xyz, d_o, n * 12, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cleanup();
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_blackbody: ") + cudaGetErrorString(e));
     return VPTC_OK;
 }
 
