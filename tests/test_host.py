@@ -448,3 +448,49 @@ def test_host_parsers_survive_mutated_input(api, scenes, tmp_path):
         (tmp_path / "m.ckpt").write_bytes(mutate(raw, 300))
         attempt(lambda: api.film_load(tmp_path / "m.ckpt", scene))
     assert outcomes["ok"] > 0
+
+
+def test_nvdb_reader_ends_on_hostile_size_fields(api, tmp_path):
+    """Size fields that point backwards, past the end of the file or at 2^64-ish values must end in an error quickly (round-1 advisor
+    finding: a raw dump whose second grid header carried gridSize = -672 rewound the reader onto offset 0 forever; a segment whose
+    fileSize was negative did the same). Runs in a child process under a timeout so that a regression is a failure, not a hang."""
+    import struct
+    import subprocess
+    import sys
+    g = api.synth_volume("fire", (16, 16, 16), 0.5, 2, None)
+    good = tmp_path / "good.nvdb"
+    g.write(good)
+    seg = good.read_bytes()
+    raw = bytes(g.density.view())
+    hdr = bytearray(raw[:672])
+    files = {}
+    a = bytearray(hdr); a[32:40] = struct.pack("<Q", 672)                    # header 1: gridSize = 672 (its own header only) ...
+    a[40:44] = b"zzz\0"                                                        # (a name that never matches)
+    b = bytearray(a); b[32:40] = struct.pack("<Q", (1 << 64) - 672)            # ... header 2: gridSize = (uint64)-672 -> rewind to 0
+    files["raw_rewind"] = bytes(a + b)
+    files["raw_huge"] = bytes(a[:32] + struct.pack("<Q", 1 << 62) + a[40:])
+    files["raw_zero"] = bytes(a[:32] + struct.pack("<Q", 0) + a[40:])
+    meta_off = 16                                                              # FileHeader is 16 B; FileMetaData.fileSize at +8
+    for label, v in (("seg_negative", (1 << 64) - (16 + 176 + 8)), ("seg_huge", 1 << 62), ("seg_zero", 0)):
+        s = bytearray(seg)
+        s[meta_off + 8:meta_off + 16] = struct.pack("<Q", v)
+        name_size = struct.unpack_from("<I", s, meta_off + 136)[0]
+        s[meta_off + 176:meta_off + 176 + name_size] = b"x" * (name_size - 1) + b"\0"  # never matches: the reader must SKIP this grid
+        files[label] = bytes(s) + seg
+    s = bytearray(seg); s[meta_off:meta_off + 8] = struct.pack("<Q", 1 << 61); files["seg_gridsize_huge"] = bytes(s)
+    for label, data in files.items():
+        (tmp_path / f"{label}.nvdb").write_bytes(data)
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from volume_path_tracer_b200 import api\n"
+            "import glob\n"
+            "for p in sorted(glob.glob(%r)):\n"
+            "    for name in ('density', 'temperature', 'nope'):\n"
+            "        try:\n"
+            "            api.VolumeGrids.read_from_file(p) if name == 'density' else api.lib().vptc_nvdb_read_grid(p.encode(), name.encode(), api.C.byref(api.C.c_void_p()), api.C.byref(api.C.c_size_t()))\n"
+            "        except api.VptError:\n"
+            "            pass\n"
+            "print('done')\n") % (str(ROOT), str(tmp_path / "*.nvdb"))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "done" in r.stdout, r.stderr[-2000:]
+    # and the well-formed file still reads
+    assert api.VolumeGrids.read_from_file(good).density.nbytes == g.density.nbytes

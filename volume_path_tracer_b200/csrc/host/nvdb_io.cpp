@@ -1,3 +1,4 @@
+#define _FILE_OFFSET_BITS 64
 // nvdb_io.cpp — read/write `.nvdb` files without the NanoVDB headers.
 //
 // Replaces nanovdb::io::readGrid<HostBuffer>(path, name) / io::writeGrids as the reference uses them
@@ -11,6 +12,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <new>
+#include <sys/types.h>
+#include <vector>
 #include <zlib.h>
 
 #include "nvdb_format.h"
@@ -44,72 +48,93 @@ static uint64_t name_key(const char* s)
     return h;
 }
 
+// Every size field comes from the file: each is checked against the bytes that remain before it is used to allocate, read or
+// skip, and every skip moves strictly forward (64-bit offsets), so a hostile file ends in an error — never in a rewind loop,
+// a giant allocation or a short read taken for a grid.
 std::string read_nvdb_grid(const std::string& path, const std::string& name, void** out, size_t* outBytes)
 {
     *out = nullptr; *outBytes = 0;
     File file; file.f = std::fopen(path.c_str(), "rb");
     if (!file.f) return "cannot open \"" + path + "\"";
     FILE* f = file.f;
+    if (fseeko(f, 0, SEEK_END) != 0) return "cannot seek in \"" + path + "\"";
+    const uint64_t file_size = uint64_t(ftello(f));
+    if (fseeko(f, 0, SEEK_SET) != 0) return "cannot seek in \"" + path + "\"";
+    uint64_t pos = 0; // offset of the next unread byte; only ever grows
+    auto remaining = [&]() { return file_size - pos; };
+    auto read_at_pos = [&](void* p, uint64_t n) { // n <= remaining() is the caller's check
+        if (!rd(f, p, size_t(n))) return false;
+        pos += n;
+        return true;
+    };
+    auto skip = [&](uint64_t n) {
+        if (n > remaining()) return false;
+        pos += n;
+        return fseeko(f, off_t(pos), SEEK_SET) == 0;
+    };
     uint64_t magic = 0;
-    if (!rd(f, &magic, 8)) return "file too short";
-    std::fseek(f, 0, SEEK_SET);
+    if (file_size < 8 || !rd(f, &magic, 8)) return "file too short";
+    if (fseeko(f, 0, SEEK_SET) != 0) return "cannot seek in \"" + path + "\"";
 
     if (magic == MAGIC_GRID) { // raw concatenated grid buffers
-        for (;;) {
+        while (remaining() >= sizeof(GridData)) {
             GridData g;
-            const long pos = std::ftell(f);
-            if (!rd(f, &g, sizeof(g))) break;
-            if (g.magic != MAGIC_GRID || g.gridSize < sizeof(GridData)) return "corrupt raw grid buffer";
-            if (name == g.gridName) {
+            const uint64_t grid_pos = pos;
+            if (!read_at_pos(&g, sizeof(g))) return "truncated grid header";
+            if (g.magic != MAGIC_GRID || g.gridSize < sizeof(GridData) || g.gridSize - sizeof(GridData) > remaining()) return "corrupt raw grid buffer";
+            if (std::memchr(g.gridName, 0, sizeof(g.gridName)) && name == g.gridName) {
                 void* p = alloc_grid(g.gridSize);
                 if (!p) return "out of memory";
-                std::fseek(f, pos, SEEK_SET);
-                if (!rd(f, p, g.gridSize)) { std::free(p); return "truncated grid"; }
+                pos = grid_pos;
+                if (fseeko(f, off_t(pos), SEEK_SET) != 0 || !read_at_pos(p, g.gridSize)) { std::free(p); return "truncated grid"; }
                 *out = p; *outBytes = g.gridSize;
                 return "";
             }
-            std::fseek(f, pos + long(g.gridSize), SEEK_SET);
+            if (!skip(g.gridSize - sizeof(GridData))) return "corrupt raw grid buffer";
         }
         return "Grid name '" + name + "' not found in file";
     }
 
-    for (;;) { // segments
+    while (remaining() >= sizeof(FileHeader)) { // segments
         FileHeader h;
-        if (!rd(f, &h, sizeof(h))) break;
+        if (!read_at_pos(&h, sizeof(h))) return "truncated segment header";
         if (h.magic != MAGIC_NUMB && h.magic != MAGIC_FILE) return "bad segment magic in \"" + path + "\"";
         if (version_major(h.version) != ABI_MAJOR) return "unsupported NanoVDB file version";
+        if (uint64_t(h.gridCount) * sizeof(FileMetaData) > remaining()) return "truncated metadata";
         std::vector<FileMetaData> metas(h.gridCount);
         std::vector<std::string> names(h.gridCount);
         for (uint16_t i = 0; i < h.gridCount; ++i) {
-            if (!rd(f, &metas[i], sizeof(FileMetaData))) return "truncated metadata";
+            if (remaining() < sizeof(FileMetaData) || !read_at_pos(&metas[i], sizeof(FileMetaData))) return "truncated metadata";
+            if (metas[i].nameSize > remaining()) return "truncated grid name";
             std::string nm(metas[i].nameSize, '\0');
-            if (metas[i].nameSize && !rd(f, nm.data(), metas[i].nameSize)) return "truncated grid name";
+            if (metas[i].nameSize && !read_at_pos(nm.data(), metas[i].nameSize)) return "truncated grid name";
             names[i] = nm.c_str(); // strip NUL
         }
         for (uint16_t i = 0; i < h.gridCount; ++i) {
             const FileMetaData& m = metas[i];
-            if (names[i] != name) { std::fseek(f, long(m.fileSize), SEEK_CUR); continue; }
-            void* p = alloc_grid(m.gridSize);
-            if (!p) return "out of memory";
-            bool ok = true;
+            if (m.fileSize == 0 || m.fileSize > remaining()) return "corrupt segment: grid payload size exceeds the file";
+            if (names[i] != name) { if (!skip(m.fileSize)) return "corrupt segment"; continue; }
+            if (m.gridSize < sizeof(GridData) || m.gridSize > (uint64_t(1) << 40)) return "corrupt segment: implausible grid size";
             std::string err;
+            void* p = nullptr;
             if (h.codec == 0) {
-                ok = rd(f, p, m.gridSize);
-                if (!ok) err = "truncated grid";
+                if (m.gridSize > remaining()) return "truncated grid";
+                if (!(p = alloc_grid(m.gridSize))) return "out of memory";
+                if (!read_at_pos(p, m.gridSize)) err = "truncated grid";
             } else if (h.codec == 1) { // ZIP (codec is taken from the segment header, NV/io/IO.h:512)
                 uint64_t csize = 0;
-                ok = rd(f, &csize, 8);
-                std::unique_ptr<uint8_t[]> tmp(ok ? new uint8_t[csize] : nullptr);
-                ok = ok && rd(f, tmp.get(), csize);
-                if (ok) {
-                    uLongf n = uLongf(m.gridSize);
-                    ok = uncompress(static_cast<Bytef*>(p), &n, tmp.get(), uLong(csize)) == Z_OK && n == m.gridSize;
-                }
-                if (!ok) err = "ZIP decode failed";
+                if (remaining() < 8 || !read_at_pos(&csize, 8) || csize == 0 || csize > remaining()) return "ZIP decode failed: bad compressed size";
+                if (m.gridSize / 1100 > csize) return "ZIP decode failed: grid size impossible for the compressed size"; // deflate expands <= ~1032x
+                std::unique_ptr<uint8_t[]> tmp(new (std::nothrow) uint8_t[csize]);
+                if (!tmp) return "out of memory";
+                if (!read_at_pos(tmp.get(), csize)) return "ZIP decode failed";
+                if (!(p = alloc_grid(m.gridSize))) return "out of memory";
+                uLongf n = uLongf(m.gridSize);
+                if (!(uncompress(static_cast<Bytef*>(p), &n, tmp.get(), uLong(csize)) == Z_OK && n == m.gridSize)) err = "ZIP decode failed";
             } else {
-                ok = false; err = "BLOSC-compressed .nvdb is not supported";
+                err = "BLOSC-compressed .nvdb is not supported";
             }
-            if (!ok) { std::free(p); return err; }
+            if (!err.empty()) { std::free(p); return err; }
             *out = p; *outBytes = m.gridSize;
             return "";
         }

@@ -67,6 +67,7 @@ int fail(vptc_ctx* c, int code, const std::string& msg)
         if (e_ != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+// Stages a baked grid into a FRESH DeviceGrid; on any failure the partial allocations are released and `g` is left empty.
 int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
 {
     g.release();
@@ -77,12 +78,16 @@ int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
         g.bytes += bytes;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
     };
-    CU(up(&g.cells, b.cells.data(), b.cells.size() * 4));
-    CU(up(&g.slots, b.slots.data(), b.slots.size() * 4));
-    CU(up(&g.tile_value, b.tile_value.data(), b.tile_value.size() * 4));
-    CU(up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4));
-    CU(up(&g.bricks, b.bricks.data(), b.bricks.size() * 4));
-    CU(cudaStreamSynchronize(ctx->stream));
+    cudaError_t e;
+    if ((e = up(&g.cells, b.cells.data(), b.cells.size() * 4)) != cudaSuccess || (e = up(&g.slots, b.slots.data(), b.slots.size() * 4)) != cudaSuccess ||
+        (e = up(&g.tile_value, b.tile_value.data(), b.tile_value.size() * 4)) != cudaSuccess ||
+        (e = up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4)) != cudaSuccess ||
+        (e = up(&g.bricks, b.bricks.data(), b.bricks.size() * 4)) != cudaSuccess || (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) {
+        cudaStreamSynchronize(ctx->stream); // the host vectors must outlive any copy still in flight
+        g.release();
+        cudaGetLastError();
+        return fail(ctx, VPTC_ERR_CUDA, std::string("staging the baked volume to the device: ") + cudaGetErrorString(e));
+    }
     g.dev.cells = static_cast<const uint32_t*>(g.cells);
     g.dev.slots = static_cast<const Slot*>(g.slots);
     g.dev.tile_value = static_cast<const float*>(g.tile_value);
@@ -96,7 +101,13 @@ int check_scene(vptc_ctx* ctx, const vptc_scene* s)
     if (!s) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "scene is null");
     if (s->output_size[0] <= 0 || s->output_size[1] <= 0 || s->tile_size[0] <= 0 || s->tile_size[1] <= 0)
         return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "output_size and tile_size must be positive");
-    if (s->tile_size[0] * s->tile_size[1] > (int64_t(1) << 20)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile too large");
+    // The kernels hold pixel coordinates in 32-bit ints and the film is W*H*16 bytes: bound every factor BEFORE multiplying, so that no
+    // product below can wrap (a [2^31, 2^31] frame used to wrap the film size to 0 and launch on a null film).
+    constexpr int64_t kMaxSide = int64_t(1) << 20, kMaxPixels = int64_t(1) << 32; // 64 Gi B of film at most
+    if (s->output_size[0] > kMaxSide || s->output_size[1] > kMaxSide || s->output_size[0] * s->output_size[1] > kMaxPixels)
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "output_size too large (each side <= 2^20, at most 2^32 pixels)");
+    if (s->tile_size[0] > kMaxSide || s->tile_size[1] > kMaxSide || s->tile_size[0] * s->tile_size[1] > (int64_t(1) << 20))
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile too large (at most 2^20 pixels per tile)");
     return VPTC_OK;
 }
 
@@ -206,23 +217,29 @@ int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_byte
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: ctx is null");
     if (!density_grid) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: the density grid is required (volume_grids.cpp:48-56)");
     CU(cudaSetDevice(ctx->device));
+    // Stage into fresh device grids and swap only when EVERYTHING succeeded: a failed call (corrupt buffer, out of device memory on a
+    // larger second volume) leaves the context rendering the previous volume, never a half-released one.
+    DeviceGrid new_density, new_temperature;
+    bool new_has_temperature = false;
     try {
-        vpt_host::BakedGrid b;
-        vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
-        int rc = upload(ctx, b, ctx->density);
-        if (rc != VPTC_OK) return rc;
-        ctx->has_temperature = false;
-        ctx->temperature.release();
+        {
+            vpt_host::BakedGrid b;
+            vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
+            if (int rc = upload(ctx, b, new_density)) return rc;
+        }
         if (temperature_grid && temperature_bytes) {
             vpt_host::BakedGrid t;
             vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t);
-            rc = upload(ctx, t, ctx->temperature);
-            if (rc != VPTC_OK) return rc;
-            ctx->has_temperature = true;
+            if (int rc = upload(ctx, t, new_temperature)) { new_density.release(); return rc; }
+            new_has_temperature = true;
         }
     } catch (const std::exception& e) {
+        new_density.release(); new_temperature.release();
         return fail(ctx, VPTC_ERR_BAD_GRID, std::string("vptc_set_volume: ") + e.what());
     }
+    ctx->density.release(); ctx->temperature.release();
+    ctx->density = new_density; ctx->temperature = new_temperature;
+    ctx->has_temperature = new_has_temperature;
     ctx->has_volume = true;
     return VPTC_OK;
 }
@@ -492,7 +509,8 @@ int vptc_blackbody(vptc_ctx* ctx, const float* temps_k, size_t n, float* xyz)
 int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image: ctx is null");
-    if (!film_xyzw || !rgb8 || width <= 0 || height <= 0) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image: bad argument");
+    if (!film_xyzw || !rgb8 || width <= 0 || height <= 0 || width > (int64_t(1) << 20) || height > (int64_t(1) << 20) || width * height > (int64_t(1) << 32))
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image: bad argument (null pointer, or a side outside 1..2^20 / more than 2^32 pixels)");
     CU(cudaSetDevice(ctx->device));
     const size_t n = size_t(width) * size_t(height);
     float* d_f = nullptr; uint8_t* d_rgb = nullptr;
