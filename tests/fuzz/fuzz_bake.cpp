@@ -28,6 +28,25 @@ int main(int argc, char** argv)
         if (out.bricks.empty() || out.cells.empty()) { std::printf("pristine grid baked to nothing\n"); return 3; }
         std::free(p);
     }
+    { // fixed corpus: finite but SINGULAR / inconsistent index<->world maps must be rejected (a zero inverse map makes every ray direction
+      // NaN on the device, whose march then never ends): all-zero invMatF, all-zero matF, a rank-2 map, matF that is not invMatF's inverse
+        const size_t MAT = 296, INV = 296 + 36; // nvdbf::GridData::map.matF / .invMatF
+        for (int c = 0; c < 4; ++c) {
+            void* p = nullptr;
+            if (posix_memalign(&p, 64, n)) return 2;
+            std::memcpy(p, s.density.data(), n);
+            uint8_t* b = static_cast<uint8_t*>(p);
+            float m[9];
+            if (c == 0) std::memset(b + INV, 0, 36);
+            else if (c == 1) std::memset(b + MAT, 0, 36);
+            else if (c == 2) { std::memcpy(m, b + INV, 36); m[6] = m[3]; m[7] = m[4]; m[8] = m[5]; std::memcpy(b + INV, m, 36); }
+            else { std::memcpy(m, b + MAT, 36); for (float& v : m) v *= 3.0f; std::memcpy(b + MAT, m, 36); }
+            bool rejected = false;
+            try { BakedGrid out; bake_grid(p, n, true, out); } catch (const std::exception&) { rejected = true; }
+            std::free(p);
+            if (!rejected) { std::printf("singular-map case %d was baked\n", c); return 4; }
+        }
+    }
     // regions worth hitting: grid/tree/root headers (first ~1 KB), root tiles, and random places in the node tables
     for (int it = 0; it < iters; ++it) {
         void* p = nullptr;

@@ -370,9 +370,33 @@ def test_errors(renderer, api, scenes):
     bad = scene.copy(); bad.tile_size[0] = 0
     with pytest.raises(api.VptError):
         renderer.run(bad, renderer.new_film(scene))
+    huge = scene.copy(); huge.output_size[0] = huge.output_size[1] = 2 ** 31  # W*H*16 wraps to 0 in 64 bits
+    with pytest.raises(api.VptError) as e:
+        renderer.run_device(huge, 16, 1, 1, 1)
+    assert e.value.code == -1
     junk = np.zeros(4096, np.uint8)
     assert api.lib().vptc_set_volume(r2._ctx, junk.ctypes.data, junk.nbytes, None, 0) == -2
     r2.close()
+
+
+def test_failed_set_volume_keeps_the_previous_volume(renderer, oracle, loaded):
+    """A rejected second vptc_set_volume (corrupt buffer) must leave the context rendering the FIRST volume (round-1 advisor finding:
+    the old volume used to be freed before the new one was validated and staged)."""
+    scene, spec, grids = loaded("fire")
+    jids = np.arange(8, dtype=np.uint64)
+    before = renderer.trace_jobs(scene, jids)
+    bad = grids.density.view().copy()
+    bad[296 + 36:296 + 72] = 0  # singular inverse map
+    import ctypes
+    rc = renderer_api_set_volume(renderer, bad)
+    assert rc == -2
+    after = renderer.trace_jobs(scene, jids)
+    assert np.array_equal(before[0], after[0]) and np.array_equal(before[1], after[1])
+
+
+def renderer_api_set_volume(renderer, density_bytes: np.ndarray) -> int:
+    from volume_path_tracer_b200 import api
+    return api.lib().vptc_set_volume(renderer._ctx, density_bytes.ctypes.data, density_bytes.nbytes, None, 0)
 
 
 @pytest.mark.parametrize("name,waves", [("fire", 48), ("wdas_cloud", 48)])

@@ -131,6 +131,22 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
     std::memcpy(h.vec, g->map.vecF, sizeof(h.vec));
     for (int i = 0; i < 9; ++i) // a NaN / infinite transform turns every ray time into NaN, and `t0 >= t1` never ends a march on NaN
         if (!std::isfinite(h.mat[i]) || !std::isfinite(h.invMat[i]) || (i < 3 && !std::isfinite(h.vec[i]))) throw std::runtime_error("bake: the grid's index<->world transform is not finite");
+    {   // ... and so does a finite but SINGULAR map (all zeros in a corrupt header): the index-space direction is 0, its normalisation 0 * inf = NaN.
+        // Require both 3x3 maps to be invertible and each other's inverse to within fp32 slack.
+        auto det3 = [](const float* m) {
+            return double(m[0]) * (double(m[4]) * m[8] - double(m[5]) * m[7]) - double(m[1]) * (double(m[3]) * m[8] - double(m[5]) * m[6]) +
+                   double(m[2]) * (double(m[3]) * m[7] - double(m[4]) * m[6]);
+        };
+        const double d_fwd = det3(h.mat), d_inv = det3(h.invMat);
+        bool ok = std::isfinite(d_fwd) && std::isfinite(d_inv) && std::fabs(d_fwd) > 1e-30 && std::fabs(d_inv) > 1e-30;
+        for (int r = 0; ok && r < 3; ++r)
+            for (int c = 0; c < 3; ++c) { // mat * invMat ~= I (NanoVDB applies them as row-vector maps; the product test is the same either way)
+                double acc = 0.0;
+                for (int k = 0; k < 3; ++k) acc += double(h.mat[r * 3 + k]) * double(h.invMat[k * 3 + c]);
+                if (!(std::fabs(acc - (r == c ? 1.0 : 0.0)) < 1e-3)) ok = false;
+            }
+        if (!ok) throw std::runtime_error("bake: the grid's index<->world transform is singular or inconsistent with its stored inverse");
+    }
     for (int a = 0; a < 3; ++a) { h.bbox_min[a] = tv.root->bbox[a]; h.bbox_max[a] = tv.root->bbox[3 + a]; }
     for (int a = 0; a < 3; ++a) // keeps every device-side coordinate sum in int32 and the cell caches' INT_MIN sentinel outside the grid
         if (h.bbox_min[a] <= h.bbox_max[a] && (h.bbox_min[a] < -(1 << 30) || h.bbox_max[a] > (1 << 30)))

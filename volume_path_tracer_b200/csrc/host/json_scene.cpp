@@ -176,7 +176,9 @@ struct Schema {
         if (!v) return false;
         if (v->kind != JValue::Array || v->arr.size() != 2) return fail("\"" + path + k + "\" must be an array of 2 integers");
         for (int i = 0; i < 2; ++i) {
-            if (v->arr[i].kind != JValue::Number || v->arr[i].num != std::floor(v->arr[i].num)) return fail("\"" + path + k + "\" must be an array of 2 integers");
+            // finite and exactly representable before the cast (int64_t(1e300) or int64_t(inf) is undefined behaviour)
+            if (v->arr[i].kind != JValue::Number || !std::isfinite(v->arr[i].num) || std::fabs(v->arr[i].num) >= 9007199254740992.0 || v->arr[i].num != std::floor(v->arr[i].num))
+                return fail("\"" + path + k + "\" must be an array of 2 integers");
             out[i] = int64_t(v->arr[i].num);
         }
         return true;
