@@ -116,6 +116,32 @@ VPTC_API int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_
 VPTC_API int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves,
                                 uint32_t wave_stride, void* d_film_xyzw);
 
+/* A slice of the (tile, wave) job space: waves first_wave + k*wave_stride, k < n_waves, of the tiles [tile_begin, tile_begin + tile_count)
+ * (row-major tile indices as TileProvider::compute_tile_rect numbers them, src/tile_provider.cpp:95-105; tile_count 0 = every tile).
+ * Job ids stay (wave-1)*ntiles + tile whatever the slice, so any partition of the job space — by waves, by tile stripes, across calls or
+ * across GPUs — renders exactly the samples one vptc_render call over the whole space would. */
+typedef struct vptc_job_range {
+    uint32_t first_wave, n_waves, wave_stride;
+    uint32_t reserved;
+    uint64_t tile_begin, tile_count;
+} vptc_job_range;
+
+/* vptc_render_device over an arbitrary job slice (blocking). */
+VPTC_API int vptc_render_device_range(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* range, void* d_film_xyzw);
+
+/* Asynchronous forms: enqueue and return. The reference's workers never stop between waves (TileProvider hands out the next wave's jobs
+ * as soon as a worker is free, src/tile_provider.cpp:27-67); a sequence of blocking calls would instead let the GPU drain at the end of
+ * every call (a job is a whole tile rendered by one lane). Calls made before vptc_wait are published to a device-side ring: the lanes of
+ * the kernel already running carry on into the next call's jobs, so many small calls run at the rate of one large one.
+ *   vptc_render_device_async: film resident on the device (may be the same film for every call).
+ *   vptc_render_async: host film; returns once the PREVIOUS async call's film has been added into its host film (that copy and add overlap
+ *     this call's rendering). The film passed to a call is complete after the next vptc_render_async or vptc_wait returns; do not read it before.
+ *   vptc_wait: everything enqueued is finished and accumulated; vptc_last_render_ms then covers the whole series.
+ * Any other call on the context waits first. A call whose scene differs from the running series' waits for the series, then starts its own. */
+VPTC_API int vptc_render_device_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* range, void* d_film_xyzw);
+VPTC_API int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw);
+VPTC_API int vptc_wait(vptc_ctx* ctx);
+
 /* Device time (CUDA events on ctx's stream) of the kernels of the last render call, milliseconds. */
 VPTC_API float vptc_last_render_ms(const vptc_ctx* ctx);
 /* Bytes of HBM the baked volume (density + temperature: cells, lower slots, tiles, apron bricks) occupies; 0 before vptc_set_volume. */

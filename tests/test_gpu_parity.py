@@ -341,7 +341,7 @@ def test_blackbody_device_bit_exact(renderer, oracle, gold):
                         [49800.5, 49899.9, 49899.996, 49900, 49900.004, 6e4, 1e5, 1e6, 3.0e38, np.inf, -np.inf, np.nan, -1, 0, 1e-30, 99.99, 100, 100.01]]).astype(np.float32)
     got, want = renderer.blackbody(T), oracle.blackbody(T)
     assert np.array_equal(got, want, equal_nan=True)
-    assert np.isnan(got[np.isinf(T) | np.isnan(T)]).all() and (got[T <= 0] == 0).all()
+    assert np.isnan(got[np.isinf(T) | np.isnan(T)]).all() and (got[(T <= 0) & np.isfinite(T)] == 0).all()
     assert (got[(T >= 49900) & (T < 1e6)] > 0).all()
 
 
@@ -509,3 +509,69 @@ def test_kernel_variants_agree(renderer, loaded, name):
         assert np.array_equal(n, res[0][1]) and np.array_equal(x, res[0][0])
         assert c == res[0][3]
         assert np.array_equal(f[..., 3], res[0][2][..., 3]) and np.allclose(f, res[0][2], rtol=1e-5, atol=1e-7)
+
+
+# ---------------------------------------------------------------- asynchronous calls, job slices (device-side range ring)
+def test_async_calls_equal_blocking_calls(renderer, loaded):
+    """vptc_render_async publishes each call into the device ring and the running kernel carries on into it; whatever the interleaving,
+    call k's film must hold exactly call k's waves. One wave per call has no add-order slack: every film is bit-equal to a blocking call's."""
+    scene, spec, grids = loaded("dense512")
+    waves = [1, 2, 3, 5, 8, 13, 21, 34]
+    blocking = [renderer.run(scene, renderer.new_film(scene), first_wave=w, n_waves=1) for w in waves]
+    films = [renderer.new_film(scene) for _ in waves]
+    for w, f in zip(waves, films):
+        renderer.run_async(scene, f, w, 1)
+    renderer.wait()
+    for a, b in zip(films, blocking):
+        assert np.array_equal(a, b)
+    # several waves per call into ONE accumulating host film, like the CLI's progressive loop
+    total = renderer.new_film(scene)
+    for first in range(1, 25, 4):
+        renderer.run_async(scene, total, first, 4)
+    renderer.wait()
+    want = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=24)
+    assert np.array_equal(total[..., 3], want[..., 3]) and (total[..., 3] == 24).all()
+    assert np.allclose(total, want, rtol=1e-5, atol=1e-7)
+    # a different scene in the middle of a series: the series is finished first, results stay per call
+    other = scene.copy(); other.seed = scene.seed + 1
+    fa, fb, fc = renderer.new_film(scene), renderer.new_film(scene), renderer.new_film(scene)
+    renderer.run_async(scene, fa, 1, 1); renderer.run_async(other, fb, 1, 1); renderer.run_async(scene, fc, 2, 1)
+    renderer.wait()
+    assert np.array_equal(fa, blocking[0]) and np.array_equal(fc, blocking[1])
+    assert np.array_equal(fb, renderer.run(other, renderer.new_film(other), first_wave=1, n_waves=1)) and not np.array_equal(fb, fa)
+    renderer.wait()  # idempotent
+
+
+def test_device_async_series_and_tile_stripes(renderer, loaded):
+    """vptc_render_device_async into one device film, and vptc_job_range tile stripes: any partition of the (tile, wave) job space — by
+    waves, by stripes of tiles, across calls — renders exactly the jobs of the whole (job ids are (wave-1)*ntiles + tile whatever the slice)."""
+    import torch
+    scene, spec, grids = loaded("fire")
+    H, W, nt = scene.height, scene.width, scene.ntiles
+    whole = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda:0")
+    renderer.run_device(scene, whole.data_ptr(), 1, 1, 1)
+    parts = torch.zeros_like(whole)
+    cuts = [0, 1, nt // 3, nt // 3, nt - 5, nt]  # includes an empty stripe
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        if b > a:
+            renderer.run_device_range(scene, parts.data_ptr(), 1, 1, 1, tile_begin=a, tile_count=b - a, wait=False)
+    renderer.wait()
+    torch.cuda.synchronize()
+    assert torch.equal(parts, whole)  # one wave: bit-equal
+    # a stripe touches only its own pixels
+    stripe = torch.zeros_like(whole)
+    ntx = -(-W // int(scene.tile_size[0]))
+    renderer.run_device_range(scene, stripe.data_ptr(), 1, 2, 1, tile_begin=ntx, tile_count=2 * ntx)  # tile rows 1 and 2
+    th = int(scene.tile_size[1])
+    assert bool((stripe[th:3 * th, :, 3] == 2).all()) and float(stripe[:th].abs().sum()) == 0 and float(stripe[3 * th:].abs().sum()) == 0
+    # waves as a series of async calls, interleaved strides
+    series = torch.zeros_like(whole)
+    for first in (1, 2, 3):
+        renderer.run_device_range(scene, series.data_ptr(), first, 4, 3, wait=False)  # waves first, first+3, ... : 12 waves in all
+    renderer.wait()
+    ref = torch.zeros_like(whole)
+    renderer.run_device(scene, ref.data_ptr(), 1, 12, 1)
+    torch.cuda.synchronize()
+    assert torch.equal(series[..., 3], ref[..., 3]) and torch.allclose(series, ref, rtol=1e-5, atol=1e-7)
+    with pytest.raises(Exception):
+        renderer.run_device_range(scene, series.data_ptr(), 1, 1, 1, tile_begin=nt - 1, tile_count=5)

@@ -81,6 +81,12 @@ class Counters(C.Structure):
         return 32 * self.density_evals + 32 * self.temperature_evals + 4 * self.majorant_fetches + 32 * self.pixel_samples
 
 
+class JobRange(C.Structure):
+    """vptc_job_range: waves first_wave + k*wave_stride (k < n_waves) of the tiles [tile_begin, tile_begin + tile_count); tile_count 0 = all."""
+    _fields_ = [("first_wave", C.c_uint32), ("n_waves", C.c_uint32), ("wave_stride", C.c_uint32), ("reserved", C.c_uint32),
+                ("tile_begin", C.c_uint64), ("tile_count", C.c_uint64)]
+
+
 class VptError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"vptc error {code}: {msg}")
@@ -88,7 +94,7 @@ class VptError(RuntimeError):
 
 
 EXPORTS = [
-    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_last_render_ms", "vptc_device_volume_bytes",
+    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_last_render_ms", "vptc_device_volume_bytes",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
@@ -116,6 +122,10 @@ def lib() -> C.CDLL:
     L.vptc_set_volume.argtypes = [vp, vp, sz, vp, sz]
     L.vptc_render.argtypes = [vp, C.POINTER(Scene), u32, u32, vp]
     L.vptc_render_device.argtypes = [vp, C.POINTER(Scene), u32, u32, u32, vp]
+    L.vptc_render_device_range.argtypes = [vp, C.POINTER(Scene), C.POINTER(JobRange), vp]
+    L.vptc_render_device_async.argtypes = [vp, C.POINTER(Scene), C.POINTER(JobRange), vp]
+    L.vptc_render_async.argtypes = [vp, C.POINTER(Scene), u32, u32, vp]
+    L.vptc_wait.argtypes = [vp]
     L.vptc_last_render_ms.argtypes = [vp]
     L.vptc_last_render_ms.restype = C.c_float
     L.vptc_device_volume_bytes.argtypes = [vp]
@@ -297,6 +307,21 @@ class Renderer:
     def run_device(self, scene: Scene, d_film_ptr: int, first_wave: int, n_waves: int, wave_stride: int = 1):
         """Same, film resident on the device (raw device pointer, e.g. torch_tensor.data_ptr())."""
         _check(lib().vptc_render_device(self._ctx, C.byref(scene), first_wave, n_waves, wave_stride, C.c_void_p(d_film_ptr)), self._ctx)
+
+    def run_device_range(self, scene: Scene, d_film_ptr: int, first_wave: int, n_waves: int, wave_stride: int = 1, tile_begin: int = 0, tile_count: int = 0,
+                         wait: bool = True):
+        """A slice of the job space (vptc_job_range) into a device film; wait=False enqueues (vptc_render_device_async) — finish with wait()."""
+        jr = JobRange(first_wave, n_waves, wave_stride, 0, tile_begin, tile_count)
+        fn = lib().vptc_render_device_range if wait else lib().vptc_render_device_async
+        _check(fn(self._ctx, C.byref(scene), C.byref(jr), C.c_void_p(d_film_ptr)), self._ctx)
+
+    def run_async(self, scene: Scene, film: np.ndarray, first_wave: int, n_waves: int):
+        """vptc_render_async: enqueue waves into the HOST film; the film is complete after the next run_async or wait()."""
+        assert film.dtype == np.float32 and film.flags.c_contiguous and film.shape == (scene.height, scene.width, 4)
+        _check(lib().vptc_render_async(self._ctx, C.byref(scene), first_wave, n_waves, _ptr(film)), self._ctx)
+
+    def wait(self):
+        _check(lib().vptc_wait(self._ctx), self._ctx)
 
     def trace_jobs(self, scene: Scene, jids):
         jids = np.ascontiguousarray(jids, dtype=np.uint64)

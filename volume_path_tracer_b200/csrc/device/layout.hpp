@@ -68,6 +68,23 @@ struct SceneDev {
     uint32_t seed;
 };
 
+// One render call's share of the (tile, wave) job space. Calls are published into a small device-side ring; the persistent render kernel
+// takes jobs from its own call's range and, when that is exhausted, carries on into the next published one instead of draining — so a
+// progressive render made of many small calls keeps every lane busy across call boundaries (DESIGN.md "launch drain"). A range may also
+// cover only a stripe of tiles [tile_begin, tile_begin + tile_count) (multi-GPU tile sharding, src/tile_provider.cpp:95-105).
+//   job j of the range:  k = j / tile_count,  tile = tile_begin + j % tile_count,  jid = (first_wave - 1 + k * wave_stride) * ntiles + tile
+constexpr unsigned RING_SLOTS = 64;
+struct RangeDesc { // 64 bytes
+    unsigned long long counter;  // next job index of the range = TileProvider::m_job_idx (tile_provider.cpp:28); device atomics only
+    unsigned long long done;     // jobs finished; the lane that makes it n_jobs raises host_done[slot]
+    unsigned long long n_jobs;   // tile_count * n_waves
+    float* film;                 // H*W*4 floats this range accumulates into
+    unsigned long long tile_begin, tile_count;
+    uint32_t first_wave, wave_stride;
+    uint32_t rid, pad_;          // absolute range number (slot = rid % RING_SLOTS)
+};
+static_assert(sizeof(RangeDesc) == 64, "RangeDesc");
+
 struct CountersDev {
     unsigned long long pixel_samples, density_evals, temperature_evals, majorant_fetches, rng_draws, scatter_events, shadow_rays;
     // warp-scheduling diagnostics of the sched kernel (COUNT builds): iterations, and per stage {times run, lanes served}

@@ -26,6 +26,11 @@ struct RenderArgs {
     CountersDev* counters;        // COUNT builds
     int sched_thresh[4];          // variant 2: lanes needed to run SETUP / HOT / - / EVAL in an iteration
     int pool_params[4];           // variant 3: {HOT passes per scheduling decision, queued slots needed to run HOT, EVAL, SETUP}
+    // variant 2 (default kernel): the job space comes from the range ring (layout.hpp RangeDesc) instead of queue / n_jobs / film
+    RangeDesc* ring;              // RING_SLOTS descriptors
+    const unsigned int* ring_tail;// absolute number of ranges published so far (written by the host while the kernel runs)
+    unsigned int range_begin;     // the range this launch was made for; its lanes start there
+    unsigned int* host_done;      // mapped pinned, RING_SLOTS words: rid + 1 once range rid is complete (may be null)
     float* trace_events;          // trace mode, optional: Logger<true> event log (worker.cpp:15-49), 8 floats per event
     unsigned long long* trace_event_count; unsigned long long trace_event_cap;
 };

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     // touches — path origin/direction/radiance, shadow transmittance, depth, the job's pixel bookkeeping, the
     // temperature grid's cell cache. That is 21 registers the hot loop does not have to carry, which is what lets
     // the kernel fit VPT_SCHED_MIN_BLOCKS resident blocks per SM without spilling.
-    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_WORDS = 21 };
+    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_RANGE = 21, C_WORDS = 22 };
     __shared__ uint32_t cold[C_WORDS][VPT_BLOCK_THREADS];
     const int lane_col = threadIdx.x;
 #define CLDF(i) __uint_as_float(cold[i][lane_col])
@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
 #define CLD3(i) mk(CLDF(i), CLDF((i) + 1), CLDF((i) + 2))
 #define CST3(i, v) do { CSTF(i, (v).x); CSTF((i) + 1, (v).y); CSTF((i) + 2, (v).z); } while (0)
     for (int i = 0; i < C_WORDS; ++i) cold[i][lane_col] = 0u; // sx = sy = x = y = 0: the first SETUP fetches a job
+    cold[C_RANGE][lane_col] = A.range_begin;                  // the range (render call) this lane takes jobs from: starts at this launch's own
     { CellCache r; r.reset(); CSTI(C_CT, r.x); CSTI(C_CT + 1, r.y); CSTI(C_CT + 2, r.z); cold[C_CT + 3][lane_col] = r.code; }
 
     // Logger<true> (worker.cpp:15-49), trace launches only: {type, 6 arguments, 0} appended in program order (callers trace ONE job)
@@ -133,7 +134,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         A.trace_xyz[slot * 3 + 0] = L.x; A.trace_xyz[slot * 3 + 1] = L.y; A.trace_xyz[slot * 3 + 2] = L.z;
                         A.trace_ndraws[slot] = rng.draws;
                     } else {
-                        film_add(A.film + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)) * 4, S.imaging_ratio * L.x, S.imaging_ratio * L.y, S.imaging_ratio * L.z);
+                        float* film = reinterpret_cast<float*>(__ldcg(reinterpret_cast<const unsigned long long*>(&A.ring[cold[C_RANGE][lane_col] % RING_SLOTS].film))); // the film of the call this job belongs to
+                        film_add(film + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)) * 4, S.imaging_ratio * L.x, S.imaging_ratio * L.y, S.imaging_ratio * L.z);
                     }
                     pixel_open = false;
                 }
@@ -141,13 +143,33 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     if (++x >= sx) { x = 0; ++y; }
                     if (y >= sy) {
                         if (COUNT) draws_total += rng.draws;
-                        j = atomicAdd(A.queue, 1ULL); // TileProvider::next(): m_job_idx.fetch_add(1)
-                        if (j >= A.n_jobs) { stage = ST_EXIT; break; }
+                        // TileProvider::next(): job = m_job_idx.fetch_add(1) (tile_provider.cpp:28) — on the current range of the ring; an exhausted
+                        // range hands over to the next published one (a later render call) instead of letting the lane drain.
+                        unsigned int rc = cold[C_RANGE][lane_col];
+                        RangeDesc* R = A.ring + (rc % RING_SLOTS);
+                        if (sy > 0) { // a job of range rc just finished: count it; the last one raises the host's completion flag
+                            __threadfence(); // this lane's film reductions before the count
+                            if (atomicAdd(&R->done, 1ULL) + 1ULL == __ldcg(&R->n_jobs)) {
+                                __threadfence_system();
+                                if (A.host_done) *reinterpret_cast<volatile unsigned int*>(A.host_done + (rc % RING_SLOTS)) = rc + 1u;
+                            }
+                            sy = 0;
+                        }
+                        for (;;) {
+                            j = atomicAdd(&R->counter, 1ULL);
+                            if (j < __ldcg(&R->n_jobs)) break;
+                            if (rc + 1u >= *reinterpret_cast<const volatile unsigned int*>(A.ring_tail)) { stage = ST_EXIT; break; } // ring dry
+                            ++rc;
+                            R = A.ring + (rc % RING_SLOTS);
+                        }
+                        cold[C_RANGE][lane_col] = rc;
+                        if (stage == ST_EXIT) { CSTI(C_SY, 0); break; }
                         uint64_t jid;
                         if (TRACE) jid = A.trace_jids[j];
                         else {
-                            const uint64_t k = j / S.ntiles, tile_k = j - k * S.ntiles;
-                            jid = (uint64_t(A.first_wave - 1) + k * A.wave_stride) * S.ntiles + tile_k;
+                            const uint64_t tcount = __ldcg(&R->tile_count);
+                            const uint64_t k = j / tcount, tile_k = __ldcg(&R->tile_begin) + (j - k * tcount);
+                            jid = (uint64_t(__ldcg(&R->first_wave) - 1u) + k * __ldcg(&R->wave_stride)) * S.ntiles + tile_k;
                         }
                         const uint64_t tile = jid % S.ntiles;
                         const int64_t tx0 = int64_t(tile % uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tile / uint64_t(S.ntx)) * S.th;

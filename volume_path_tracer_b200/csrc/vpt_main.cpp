@@ -116,18 +116,25 @@ int main(int argc, char* argv[])
         if (ckpt && vptc_film_save(ckpt, &cfg, film.data(), next_wave) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
     };
 
+    // The render loop. Calls are ASYNCHRONOUS (vptc_render_async): call k+1 is handed to the GPU before call k's film is brought home, and the
+    // running kernel carries on into it, so the device never drains between calls (the reference's workers never stop between waves either,
+    // tile_provider.cpp:27-67). When vptc_render_async(k+1) returns, `film` holds every wave of the calls up to k: that is the state the
+    // periodic save writes (PNG + checkpoint with next_wave = first wave of call k+1) — no pipeline flush for a save.
     const auto start = std::chrono::high_resolution_clock::now();
     double device_ms = 0.0;
-    uint32_t wave = first_wave;
+    uint32_t wave = first_wave;      // first wave not yet handed to the GPU
+    uint32_t in_film = first_wave;   // first wave not yet accumulated in `film`
     while (wave <= cfg.num_waves && !g_stop) {
         uint32_t n = std::min(per_call, cfg.num_waves - wave + 1);
         if (save_every) n = std::min(n, save_every - (wave - 1) % save_every); // calls end on multiples of K
         vptINFO("Starting wave " << wave << "/" << cfg.num_waves);
-        if (vptc_render(ctx, &cfg, wave, n, film.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
-        device_ms += vptc_last_render_ms(ctx);
+        if (vptc_render_async(ctx, &cfg, wave, n, film.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+        in_film = wave; // the previous calls are in `film` now; this one is on the device
         wave += n;
-        if (save_every && (wave - 1) % save_every == 0 && wave <= cfg.num_waves) save(wave);
+        if (save_every && in_film > first_wave && (in_film - 1) % save_every == 0) save(in_film);
     }
+    if (vptc_wait(ctx) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+    device_ms = vptc_last_render_ms(ctx);
     if (g_stop && wave <= cfg.num_waves) vptINFO("Stopped at wave " << wave - 1 << "/" << cfg.num_waves);
     const auto elapsed = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - start);
     const double rendered = double(W) * double(H) * double(wave - first_wave);

@@ -7,7 +7,9 @@
 #include <cstring>
 #include <exception>
 #include <memory>
+#include <chrono>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -48,9 +50,23 @@ struct vptc_ctx {
     float last_ms = 0.0f;
     vptc_counters last_counters{};
     int num_sms = 0;
-    // scratch film for the host-buffer path
-    float* film = nullptr; size_t film_floats = 0;
+    // ---- range ring (device/layout.hpp RangeDesc): every render call of the default kernel is published here ----
+    cudaStream_t ctl = nullptr;      // non-blocking stream: ring publication, film zeroing and staging copies run BESIDE the render kernel
+    cudaEvent_t ev_ctl = nullptr;
+    RangeDesc* d_ring = nullptr; unsigned int* d_tail = nullptr;
+    RangeDesc* h_ring = nullptr; unsigned int* h_tail = nullptr; // pinned staging, one slot per ring slot
+    unsigned int* h_done = nullptr; unsigned int* d_done = nullptr; // mapped pinned completion flags (host pointer / device alias)
+    unsigned int n_ranges = 0;       // ranges published so far (absolute range number of the next one)
+    // open series of asynchronous launches (vptc_render_device_async / vptc_render_async ... vptc_wait)
+    bool series_open = false; int series_launches = 0;
+    SceneDev series_scene{};         // a call joins the running series only when it renders the same scene
+    cudaEvent_t ev_series = nullptr; // recorded before the first launch of the series
+    // host-film path: two device films + pinned staging; at most one call's film is still on the device
+    float* film[2] = {nullptr, nullptr}; size_t film_floats = 0;
     float* pinned = nullptr; size_t pinned_floats = 0;
+    struct Pending { bool active = false; unsigned int rid = 0; float* host_film = nullptr; size_t n = 0; int buf = 0; } pending;
+    int next_buf = 0;
+    cudaEvent_t ev_launch[2] = {nullptr, nullptr}; // after the kernel launched for the call using film[b]
 };
 
 namespace {
@@ -111,8 +127,35 @@ int check_scene(vptc_ctx* ctx, const vptc_scene* s)
     return VPTC_OK;
 }
 
-// Launch the megakernel over n_jobs jobs and wait; fills last_ms / counters.
-int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace)
+// What one render call covers. tile_count == 0 means every tile of the frame.
+struct RangeSpec {
+    float* film = nullptr;
+    unsigned long long n_jobs = 0, tile_begin = 0, tile_count = 0;
+    uint32_t first_wave = 1, wave_stride = 1;
+};
+
+// Publish a range into the device ring (descriptor first, then the tail, both on the control stream, which runs beside any render kernel
+// already in flight: that kernel's lanes carry on into the new range as soon as they see the tail move). -> absolute range number in *rid.
+int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
+{
+    const unsigned int id = ctx->n_ranges, slot = id % RING_SLOTS;
+    RangeDesc& d = ctx->h_ring[slot];
+    d.counter = 0; d.done = 0; d.n_jobs = r.n_jobs; d.film = r.film;
+    d.tile_begin = r.tile_begin; d.tile_count = r.tile_count;
+    d.first_wave = r.first_wave; d.wave_stride = r.wave_stride; d.rid = id; d.pad_ = 0;
+    ctx->h_tail[slot] = id + 1;
+    ctx->h_done[slot] = 0;
+    CU(cudaMemcpyAsync(ctx->d_ring + slot, &d, sizeof(RangeDesc), cudaMemcpyHostToDevice, ctx->ctl));
+    CU(cudaMemcpyAsync(ctx->d_tail, ctx->h_tail + slot, sizeof(unsigned int), cudaMemcpyHostToDevice, ctx->ctl));
+    CU(cudaEventRecord(ctx->ev_ctl, ctx->ctl));
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_ctl, 0)); // this call's own launch starts after its range is visible
+    ctx->n_ranges = id + 1;
+    *rid = id;
+    return VPTC_OK;
+}
+
+// Enqueue the megakernel for one range on the render stream; does not wait. `full_grid`: a launch that later calls may join needs every SM.
+int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeSpec r, bool trace, bool full_grid, unsigned int* rid_out = nullptr)
 {
     vpt_host::prepare_scene(*scene, ctx->has_temperature, A.scene);
     A.density = ctx->density.dev;
@@ -121,22 +164,39 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     A.queue = ctx->queue;
     A.counters = ctx->counters;
     for (int i = 0; i < 4; ++i) A.sched_thresh[i] = std::max(1, ctx->sched_thresh[i]); // the kernel relies on >= 1
-    CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
-    if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
-    for (int i = 0; i < 4; ++i) A.pool_params[i] = ctx->pool_params[i];
-    for (int i = 0; i < 4; ++i) A.pool_params[i] = std::max(1, A.pool_params[i]);
+    for (int i = 0; i < 4; ++i) A.pool_params[i] = std::max(1, ctx->pool_params[i]);
+    if (r.tile_count == 0) { r.tile_begin = 0; r.tile_count = A.scene.ntiles; }
+    if (!trace && (r.tile_begin > A.scene.ntiles || r.tile_count > A.scene.ntiles - r.tile_begin))
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile range outside the frame's tiles");
     // variant 3 packs pixel coordinates into 16-bit halves of its slot words: larger frames / tiles take variant 2
-    const int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
+    int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
+    if (variant != 2 && !trace && r.tile_count != A.scene.ntiles) variant = 2; // tile stripes exist in the default kernel only
     int per_sm = render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
-    // persistent grid: every SM filled to its occupancy limit, never more blocks than jobs need
+    if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
+    if (variant == 2) {
+        unsigned int rid = 0;
+        if (int rc = publish_range(ctx, r, &rid)) return rc;
+        A.ring = ctx->d_ring; A.ring_tail = ctx->d_tail; A.range_begin = rid; A.host_done = ctx->d_done;
+        if (rid_out) *rid_out = rid;
+    } else {
+        A.film = r.film; A.n_jobs = r.n_jobs; A.first_wave = r.first_wave; A.wave_stride = r.wave_stride;
+        CU(cudaMemsetAsync(ctx->queue, 0, sizeof(unsigned long long), ctx->stream));
+    }
+    // persistent grid: every SM filled to its occupancy limit, never more blocks than the jobs of a stand-alone call need
     const unsigned long long per_block = (unsigned long long)(render_jobs_per_block(variant));
-    unsigned long long want = (A.n_jobs + per_block - 1) / per_block;
-    int blocks = int(std::min<unsigned long long>(want ? want : 1ULL, (unsigned long long)(ctx->num_sms) * per_sm));
+    const unsigned long long want = (r.n_jobs + per_block - 1) / per_block, full = (unsigned long long)(ctx->num_sms) * per_sm;
+    const int blocks = int(full_grid ? full : std::min<unsigned long long>(want ? want : 1ULL, full));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     CU(launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    return VPTC_OK;
+}
+
+// Wait for the launch enqueue_render made; fills last_ms / counters.
+int finish_render(vptc_ctx* ctx)
+{
     CU(cudaEventSynchronize(ctx->ev1));
     CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
     if (ctx->count) {
@@ -154,6 +214,91 @@ int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, bool trace
     return VPTC_OK;
 }
 
+int run_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, const RangeSpec& r, bool trace)
+{
+    if (int rc = enqueue_render(ctx, scene, A, r, trace, /*full_grid=*/false)) return rc;
+    return finish_render(ctx);
+}
+
+// Add `src` into `dst` (n floats) on a few host threads: the reference's film accumulates (worker.cpp:203-204), so a call's device film is
+// ADDED into the caller's host film. 8.3 M floats at 1080p, 33 M at 4K: memory bound, ~1 ms per 10 M floats on 8 threads.
+void host_add(float* dst, const float* src, size_t n)
+{
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t nt = std::min<size_t>({size_t(8), size_t(hw), n / (size_t(1) << 18) + 1});
+    auto work = [=](size_t a, size_t b) { for (size_t i = a; i < b; ++i) dst[i] += src[i]; };
+    if (nt <= 1) { work(0, n); return; }
+    std::vector<std::thread> th;
+    const size_t chunk = (n + nt - 1) / nt;
+    for (size_t t = 1; t < nt; ++t) th.emplace_back(work, std::min(n, t * chunk), std::min(n, (t + 1) * chunk));
+    work(0, std::min(n, chunk));
+    for (auto& t : th) t.join();
+}
+
+// The film of the pending host-film call is complete on the device (its range's completion flag is up, or the launch made for it has
+// finished): bring it to the host and add it into that call's film. The next call's kernel keeps running meanwhile.
+int collect_pending(vptc_ctx* ctx)
+{
+    if (!ctx->pending.active) return VPTC_OK;
+    vptc_ctx::Pending p = ctx->pending;
+    ctx->pending.active = false;
+    const unsigned int slot = p.rid % RING_SLOTS;
+    for (unsigned spin = 0;; ++spin) {
+        if (*reinterpret_cast<volatile unsigned int*>(ctx->h_done + slot) == p.rid + 1u) break;
+        const cudaError_t q = cudaEventQuery(ctx->ev_launch[p.buf]);
+        if (q == cudaSuccess) break; // the kernel launched for this range has exited: the range is complete
+        if (q != cudaErrorNotReady) return fail(ctx, VPTC_ERR_CUDA, std::string("render kernel failed: ") + cudaGetErrorString(q));
+        if (spin > 64) std::this_thread::sleep_for(std::chrono::microseconds(50));
+    }
+    CU(cudaMemcpyAsync(ctx->pinned, ctx->film[p.buf], p.n * sizeof(float), cudaMemcpyDeviceToHost, ctx->ctl));
+    CU(cudaStreamSynchronize(ctx->ctl));
+    host_add(p.host_film, ctx->pinned, p.n);
+    return VPTC_OK;
+}
+
+// Close the open series of asynchronous calls: collect the pending host film, wait for every launch, total device time.
+int wait_all(vptc_ctx* ctx)
+{
+    int rc = collect_pending(ctx);
+    if (ctx->series_open) {
+        ctx->series_open = false; ctx->series_launches = 0;
+        cudaError_t e = cudaEventSynchronize(ctx->ev1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ctx->last_ms, ctx->ev_series, ctx->ev1);
+        if (e != cudaSuccess && rc == VPTC_OK) rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_wait: ") + cudaGetErrorString(e));
+    }
+    return rc;
+}
+
+// Common front of the asynchronous render calls: argument checks, joins (or opens) the series, enqueues one launch for the range.
+int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* jr, float* d_film, unsigned int* rid)
+{
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (!jr || !d_film || jr->first_wave < 1 || jr->wave_stride < 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "render: film or range null, first_wave < 1 or wave_stride < 1");
+    CU(cudaSetDevice(ctx->device));
+    SceneDev sd; vpt_host::prepare_scene(*scene, ctx->has_temperature, sd);
+    const bool joinable = ctx->variant == 2 && !ctx->count;
+    // a call may ride on the running kernel only if that kernel renders the same scene; and the ring must never wrap onto a live range
+    if (ctx->series_open && (!joinable || std::memcmp(&sd, &ctx->series_scene, sizeof(SceneDev)) != 0 || ctx->series_launches >= int(RING_SLOTS) / 2))
+        if (int rc = wait_all(ctx)) return rc;
+    RangeSpec r;
+    r.film = d_film; r.first_wave = jr->first_wave; r.wave_stride = jr->wave_stride;
+    r.tile_begin = jr->tile_begin; r.tile_count = jr->tile_count ? jr->tile_count : sd.ntiles;
+    if (r.tile_begin > sd.ntiles || r.tile_count > sd.ntiles - r.tile_begin) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "render: tile range outside the frame's tiles");
+    r.n_jobs = r.tile_count * (unsigned long long)jr->n_waves;
+    if (r.n_jobs == 0) { if (rid) *rid = ~0u; return VPTC_OK; }
+    if (!ctx->series_open) {
+        CU(cudaEventRecord(ctx->ev_series, ctx->stream));
+        std::memset(&ctx->series_scene, 0, sizeof(SceneDev)); // padding bytes take part in the memcmp above
+        ctx->series_scene = sd;
+    }
+    RenderArgs A{};
+    unsigned int id = ~0u;
+    if (int rc = enqueue_render(ctx, scene, A, r, /*trace=*/false, /*full_grid=*/joinable, &id)) return rc;
+    ctx->series_open = true; ++ctx->series_launches;
+    if (rid) *rid = id;
+    return VPTC_OK;
+}
 } // namespace
 
 extern "C" {
@@ -184,6 +329,19 @@ int vptc_create(vptc_ctx** out, int device)
     CU(cudaMemset(ctx->bb_table, 0, 1504 * sizeof(float)));
     CU(cudaMalloc(&ctx->queue, sizeof(unsigned long long)));
     CU(cudaMalloc(&ctx->counters, sizeof(CountersDev)));
+    CU(cudaStreamCreateWithFlags(&ctx->ctl, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ctx->ev_ctl, cudaEventDisableTiming));
+    CU(cudaEventCreate(&ctx->ev_series));
+    for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&ctx->ev_launch[b], cudaEventDisableTiming));
+    CU(cudaMalloc(&ctx->d_ring, sizeof(RangeDesc) * RING_SLOTS));
+    CU(cudaMemset(ctx->d_ring, 0, sizeof(RangeDesc) * RING_SLOTS));
+    CU(cudaMalloc(&ctx->d_tail, sizeof(unsigned int)));
+    CU(cudaMemset(ctx->d_tail, 0, sizeof(unsigned int)));
+    CU(cudaMallocHost(&ctx->h_ring, sizeof(RangeDesc) * RING_SLOTS));
+    CU(cudaMallocHost(&ctx->h_tail, sizeof(unsigned int) * RING_SLOTS));
+    CU(cudaHostAlloc(&ctx->h_done, sizeof(unsigned int) * RING_SLOTS, cudaHostAllocMapped));
+    std::memset(ctx->h_done, 0, sizeof(unsigned int) * RING_SLOTS);
+    CU(cudaHostGetDevicePointer(&ctx->d_done, ctx->h_done, 0));
     std::vector<float> bb(1500);
     vpt_host::compute_blackbody_table(bb.data()); // init_blackbody_radiation_xyz (main.cpp:32)
     CU(cudaMemcpy(ctx->bb_table, bb.data(), 1500 * sizeof(float), cudaMemcpyHostToDevice));
@@ -204,8 +362,18 @@ void vptc_destroy(vptc_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     ctx->density.release(); ctx->temperature.release();
-    cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->ctl) cudaStreamSynchronize(ctx->ctl);
+    cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film[0]); cudaFree(ctx->film[1]);
+    cudaFree(ctx->d_ring); cudaFree(ctx->d_tail);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
+    if (ctx->h_tail) cudaFreeHost(ctx->h_tail);
+    if (ctx->h_done) cudaFreeHost(ctx->h_done);
+    if (ctx->ev_ctl) cudaEventDestroy(ctx->ev_ctl);
+    if (ctx->ev_series) cudaEventDestroy(ctx->ev_series);
+    for (int b = 0; b < 2; ++b) if (ctx->ev_launch[b]) cudaEventDestroy(ctx->ev_launch[b]);
+    if (ctx->ctl) cudaStreamDestroy(ctx->ctl);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -217,6 +385,8 @@ int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_byte
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: ctx is null");
     if (!density_grid) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: the density grid is required (volume_grids.cpp:48-56)");
     CU(cudaSetDevice(ctx->device));
+    if (int rc = wait_all(ctx)) return rc; // nothing may still be rendering the volume about to be replaced
+    CU(cudaStreamSynchronize(ctx->stream));
     // Stage into fresh device grids and swap only when EVERYTHING succeeded: a failed call (corrupt buffer, out of device memory on a
     // larger second volume) leaves the context rendering the previous volume, never a half-released one.
     DeviceGrid new_density, new_temperature;
@@ -244,50 +414,80 @@ int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_byte
     return VPTC_OK;
 }
 
+int vptc_wait(vptc_ctx* ctx)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_wait: ctx is null");
+    CU(cudaSetDevice(ctx->device));
+    return wait_all(ctx);
+}
+
+int vptc_render_device_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* range, void* d_film)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device_async: ctx is null");
+    return enqueue_async(ctx, scene, range, static_cast<float*>(d_film), nullptr);
+}
+
+int vptc_render_device_range(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* range, void* d_film)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device_range: ctx is null");
+    if (int rc = wait_all(ctx)) return rc;
+    ctx->last_ms = 0.0f;
+    if (int rc = enqueue_async(ctx, scene, range, static_cast<float*>(d_film), nullptr)) return rc;
+    if (!ctx->series_open) return VPTC_OK; // empty range
+    ctx->series_open = false; ctx->series_launches = 0;
+    return finish_render(ctx);
+}
+
 int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, uint32_t wave_stride, void* d_film)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device: ctx is null");
-    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    const vptc_job_range jr{first_wave, n_waves, wave_stride, 0, 0, 0};
+    return vptc_render_device_range(ctx, scene, &jr, d_film);
+}
+
+int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_async: ctx is null");
     if (int rc = check_scene(ctx, scene)) return rc;
-    if (!d_film || first_wave < 1 || wave_stride < 1) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device: film null, first_wave < 1 or wave_stride < 1");
+    if (!film_xyzw) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_async: film is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
     CU(cudaSetDevice(ctx->device));
-    ctx->last_ms = 0.0f;
-    if (n_waves == 0) return VPTC_OK;
-    RenderArgs A{};
-    A.film = static_cast<float*>(d_film);
-    A.first_wave = first_wave; A.wave_stride = wave_stride;
-    vptd::SceneDev tmp; vpt_host::prepare_scene(*scene, ctx->has_temperature, tmp);
-    A.n_jobs = tmp.ntiles * (unsigned long long)n_waves;
-    return run_render(ctx, scene, A, /*trace=*/false);
+    const size_t n = size_t(scene->output_size[0]) * size_t(scene->output_size[1]) * 4;
+    if (ctx->film_floats < n || ctx->pinned_floats < n) { // (re)size the two device films and the pinned staging buffer: nothing may be in flight
+        if (int rc = wait_all(ctx)) return rc;
+        CU(cudaStreamSynchronize(ctx->stream));
+        for (int b = 0; b < 2; ++b) { cudaFree(ctx->film[b]); ctx->film[b] = nullptr; }
+        ctx->film_floats = 0;
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr; ctx->pinned_floats = 0;
+        for (int b = 0; b < 2; ++b) CU(cudaMalloc(&ctx->film[b], n * sizeof(float)));
+        ctx->film_floats = n;
+        CU(cudaMallocHost(&ctx->pinned, n * sizeof(float)));
+        ctx->pinned_floats = n;
+    }
+    // The device renders this call's waves into a zeroed film of its own; the host later ADDS it into the caller's film, which keeps the
+    // reference's "film accumulates" contract without uploading the old film. Buffer b was last used two calls ago and has been collected.
+    const int b = ctx->next_buf;
+    CU(cudaMemsetAsync(ctx->film[b], 0, n * sizeof(float), ctx->ctl)); // ordered before the range is published (same stream)
+    const vptc_job_range jr{first_wave, n_waves, 1, 0, 0, 0};
+    unsigned int rid = ~0u;
+    if (int rc = enqueue_async(ctx, scene, &jr, ctx->film[b], &rid)) return rc;
+    if (rid == ~0u) return VPTC_OK; // nothing to render
+    CU(cudaEventRecord(ctx->ev_launch[b], ctx->stream));
+    // now that the GPU has this call's work, bring home the previous call's film (its range completes while this one is already running)
+    const int rc = collect_pending(ctx);
+    ctx->pending.active = true; ctx->pending.rid = rid; ctx->pending.host_film = film_xyzw; ctx->pending.n = n; ctx->pending.buf = b;
+    ctx->next_buf ^= 1;
+    return rc;
 }
 
 int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render: ctx is null");
-    if (int rc = check_scene(ctx, scene)) return rc;
-    if (!film_xyzw) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render: film is null");
-    CU(cudaSetDevice(ctx->device));
-    const size_t n = size_t(scene->output_size[0]) * size_t(scene->output_size[1]) * 4;
-    if (ctx->film_floats < n) {
-        cudaFree(ctx->film); ctx->film = nullptr; ctx->film_floats = 0;
-        CU(cudaMalloc(&ctx->film, n * sizeof(float)));
-        ctx->film_floats = n;
-    }
-    if (ctx->pinned_floats < n) {
-        if (ctx->pinned) cudaFreeHost(ctx->pinned);
-        ctx->pinned = nullptr; ctx->pinned_floats = 0;
-        CU(cudaMallocHost(&ctx->pinned, n * sizeof(float)));
-        ctx->pinned_floats = n;
-    }
-    // The device renders this call's waves into a zeroed film; the host then ADDS it into the caller's
-    // film, which keeps the reference's "film accumulates" contract without uploading the old film.
-    CU(cudaMemsetAsync(ctx->film, 0, n * sizeof(float), ctx->stream));
-    const int rc = vptc_render_device(ctx, scene, first_wave, n_waves, 1, ctx->film);
-    if (rc != VPTC_OK) return rc;
-    CU(cudaMemcpyAsync(ctx->pinned, ctx->film, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    for (size_t i = 0; i < n; ++i) film_xyzw[i] += ctx->pinned[i];
-    return VPTC_OK;
+    if (int rc = wait_all(ctx)) return rc;
+    ctx->last_ms = 0.0f;
+    if (int rc = vptc_render_async(ctx, scene, first_wave, n_waves, film_xyzw)) return rc;
+    return wait_all(ctx);
 }
 
 float vptc_last_render_ms(const vptc_ctx* ctx) { return ctx ? ctx->last_ms : 0.0f; }
@@ -296,6 +496,7 @@ uint64_t vptc_device_volume_bytes(const vptc_ctx* ctx) { return ctx && ctx->has_
 int vptc_enable_counters(vptc_ctx* ctx, int enabled)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_enable_counters: ctx is null");
+    if (int rc = wait_all(ctx)) return rc;
     ctx->count = enabled != 0;
     return VPTC_OK;
 }
@@ -303,6 +504,7 @@ int vptc_set_kernel_variant(vptc_ctx* ctx, int variant)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: ctx is null");
     if (variant < 0 || variant > 3) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_kernel_variant: 0 (nested), 1 (flat), 2 (flat + stage scheduling) or 3 (per-warp job pool)");
+    if (int rc = wait_all(ctx)) return rc;
     ctx->variant = variant;
     return VPTC_OK;
 }
@@ -332,9 +534,10 @@ int vptc_trace_jobs(vptc_ctx* ctx, const vptc_scene* scene, const uint64_t* jids
     cudaMemsetAsync(d_xyz, 0, slots * 12, ctx->stream);
     cudaMemsetAsync(d_nd, 0, slots * 4, ctx->stream);
     RenderArgs A{};
-    A.n_jobs = n_jobs; A.first_wave = 1; A.wave_stride = 1;
+    RangeSpec rs; rs.n_jobs = n_jobs;
     A.trace_jids = d_jids; A.trace_xyz = d_xyz; A.trace_ndraws = d_nd;
-    int rc = run_render(ctx, scene, A, /*trace=*/true);
+    int rc = wait_all(ctx);
+    if (rc == VPTC_OK) rc = run_render(ctx, scene, A, rs, /*trace=*/true);
     if (rc == VPTC_OK) {
         e = cudaMemcpy(per_pixel_xyz, d_xyz, slots * 12, cudaMemcpyDeviceToHost);
         if (e == cudaSuccess) e = cudaMemcpy(per_pixel_ndraws, d_nd, slots * 4, cudaMemcpyDeviceToHost);
@@ -365,12 +568,13 @@ int vptc_trace_path_log(vptc_ctx* ctx, const vptc_scene* scene_in, uint64_t jid,
     cudaMemcpyAsync(d_jid, &jid, 8, cudaMemcpyHostToDevice, ctx->stream);
     cudaMemsetAsync(d_n, 0, 8, ctx->stream);
     RenderArgs A{};
-    A.n_jobs = 1; A.first_wave = 1; A.wave_stride = 1;
+    RangeSpec rs; rs.n_jobs = 1;
     A.trace_jids = d_jid; A.trace_xyz = d_xyz; A.trace_ndraws = d_nd;
     A.trace_events = d_ev; A.trace_event_count = d_n; A.trace_event_cap = cap;
     const int variant = ctx->variant;
     ctx->variant = 2; // the event hooks live in the default kernel
-    int rc = run_render(ctx, &scene, A, /*trace=*/true);
+    int rc = wait_all(ctx);
+    if (rc == VPTC_OK) rc = run_render(ctx, &scene, A, rs, /*trace=*/true);
     ctx->variant = variant;
     if (rc == VPTC_OK) {
         unsigned long long n = 0;
