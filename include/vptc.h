@@ -142,6 +142,32 @@ VPTC_API int vptc_render_device_async(vptc_ctx* ctx, const vptc_scene* scene, co
 VPTC_API int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw);
 VPTC_API int vptc_wait(vptc_ctx* ctx);
 
+/* ---- several GPUs behind one handle ----
+ * Replaces the reference's worker pool as a whole: src/main.cpp:63-87 spawns num_workers threads that share ONE TileProvider, ONE Volume and
+ * ONE film. A group is that, with GPUs for workers: one host thread drives every listed device, the baked volume is replicated in each
+ * device's HBM (baked once on the host), the (tile, wave) job space is partitioned statically, and the films are combined on the first
+ * device over peer memory (NVLink / NVSwitch):
+ *   VPTC_SHARD_WAVES  device g of G renders waves first + g, first + g + G, ... of the whole frame; the partial films are SUMMED by a kernel on
+ *                     the first device that reads the other films in place through peer mappings (progressive rendering, high spp);
+ *   VPTC_SHARD_TILES  device g renders all waves of one stripe of tile rows (src/tile_provider.cpp:95-105); the stripes are GATHERED with
+ *                     peer copies: disjoint pixels, 1/G of the film each (low spp, large frames).
+ * Job ids are those of the single-device render either way, so sample counts are equal and radiance differs only by fp32 add order.
+ * vptc_group_render_async enqueues on every device and returns; vptc_group_wait finishes everything enqueued since the last wait, combines
+ * and ADDS the result into the caller's host film. vptc_group_render = both. Frame size and sharding must not change between waits. */
+typedef struct vptc_group vptc_group;
+enum { VPTC_SHARD_WAVES = 0, VPTC_SHARD_TILES = 1 };
+VPTC_API int  vptc_group_create(vptc_group** out, const int* devices, int n_devices);
+VPTC_API void vptc_group_destroy(vptc_group* group);
+VPTC_API const char* vptc_group_last_error(const vptc_group* group);
+VPTC_API int  vptc_group_size(const vptc_group* group);
+VPTC_API int  vptc_group_peer_mapped(const vptc_group* group); /* devices the first one reads directly; the others are staged by a peer copy */
+VPTC_API int  vptc_group_set_volume(vptc_group* group, const void* density_grid, size_t density_bytes, const void* temperature_grid, size_t temperature_bytes);
+VPTC_API int  vptc_group_render(vptc_group* group, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, int sharding, float* film_xyzw);
+VPTC_API int  vptc_group_render_async(vptc_group* group, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, int sharding);
+VPTC_API int  vptc_group_wait(vptc_group* group, float* film_xyzw);
+VPTC_API float vptc_group_last_render_ms(const vptc_group* group); /* slowest device of the last vptc_group_wait */
+VPTC_API vptc_ctx* vptc_group_context(vptc_group* group, int index); /* one device's context (hooks, counters); owned by the group */
+
 /* Device time (CUDA events on ctx's stream) of the kernels of the last render call, milliseconds. */
 VPTC_API float vptc_last_render_ms(const vptc_ctx* ctx);
 /* Bytes of HBM the baked volume (density + temperature: cells, lower slots, tiles, apron bricks) occupies; 0 before vptc_set_volume. */
@@ -199,7 +225,12 @@ VPTC_API int vptc_blackbody(vptc_ctx* ctx, const float* temps_k, size_t n, float
  * sRGB OETF -> clamp -> *255 -> truncate, on the device, byte-identical to the host code (glibc-exact powf). Host film in, host RGB8 out. */
 VPTC_API int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8);
 
-/* ---- host-side helpers (no GPU needed) ---- */
+/* ---- host-side helpers (no GPU needed) ----
+ * Everything from here on is plain host code. It is exported by libvptcuda.so and, without any CUDA dependency, by libvpthost.so (the same
+ * objects linked alone), so that tools which only need the scene reader, the .nvdb reader/writer, the procedural volumes or the PNG writer —
+ * e.g. the CPU baseline arm of bench.py — never map the CUDA library. The message of a failed helper is in the calling thread's context-less
+ * error slot: vptc_last_error(NULL), or vptc_host_last_error() which both libraries export. */
+VPTC_API const char* vptc_host_last_error(void);
 /* Replaces read_configuration (src/configuration.cpp:8-22): all keys mandatory. volume_path is
  * copied (relative, as written in the file) into volume_path_out. */
 VPTC_API int vptc_scene_from_json_file(const char* path, vptc_scene* out, char* volume_path_out, size_t volume_path_cap);

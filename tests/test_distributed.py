@@ -16,7 +16,8 @@ from conftest import ROOT
 
 
 def test_shard_waves_partition():
-    from volume_path_tracer_b200.distributed import shard_tiles, shard_waves
+    from volume_path_tracer_b200 import scenes
+    from volume_path_tracer_b200.distributed import shard_tile_rows, shard_waves
     for first, n, world in [(1, 8, 2), (1, 7, 4), (5, 3, 8), (1, 0, 2), (3, 1, 1), (1, 4096, 8)]:
         seen = []
         for r in range(world):
@@ -24,10 +25,16 @@ def test_shard_waves_partition():
             assert s == world
             seen += [f + k * s for k in range(c)]
         assert sorted(seen) == list(range(first, first + n)), (first, n, world)
-    for nt, world in [(11000, 8), (7, 4), (3, 8)]:
-        spans = [shard_tiles(nt, r, world) for r in range(world)]
-        assert spans[0][0] == 0 and spans[-1][1] == nt
-        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    for size, tile, world in [((700, 1000), (8, 8), 8), ((61, 29), (8, 8), 2), ((64, 16), (8, 8), 8), ((97, 55), (13, 7), 3)]:
+        scene, _ = scenes.small_variant("fire", size, 1, 0.25)
+        scene.tile_size[0], scene.tile_size[1] = tile
+        spans = [shard_tile_rows(scene, r, world) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][0] + spans[-1][1] == scene.ntiles          # tiles: contiguous, complete
+        assert all(a[0] + a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        assert spans[0][2] == 0 and spans[-1][3] == size[1]                                # film rows: contiguous bands
+        assert all(a[3] == b[2] for a, b in zip(spans, spans[1:]))
+        ntx = -(-size[0] // tile[0])
+        assert all(tb % ntx == 0 and tc % ntx == 0 and y0 == min(size[1], tb // ntx * tile[1]) for tb, tc, y0, y1 in spans)
     with pytest.raises(ValueError):
         shard_waves(0, 4, 0, 2)
     with pytest.raises(ValueError):
@@ -41,8 +48,16 @@ def _worker(rank, world, port, out_path):
     import torch.distributed as dist
     from oracle import oracle_lib
     from volume_path_tracer_b200 import api, scenes
-    from volume_path_tracer_b200.distributed import reduce_film, shard_waves
+    from volume_path_tracer_b200.distributed import gather_film_stripes, reduce_film, render_sharded, shard_tile_rows, shard_waves
     dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    class OracleRenderer:  # stand-in with the Renderer's device-film call: what is under test is the sharding + the collectives
+        def __init__(self, vol): self.vol = vol
+        def run_device(self, scene, ptr, first, count, stride):
+            import ctypes
+            f = np.ctypeslib.as_array((ctypes.c_float * (scene.height * scene.width * 4)).from_address(ptr)).reshape(scene.height, scene.width, 4)
+            for k in range(count):
+                self.vol.render(scene, f, first_wave=first + k * stride, n_waves=1, threads=2)
     try:
         scene, spec = scenes.small_variant("fire", (40, 32), 5, 0.2)
         grids = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
@@ -53,10 +68,22 @@ def _worker(rank, world, port, out_path):
             vol.render(scene, film, first_wave=first + k * stride, n_waves=1, threads=2)
         t = torch.from_numpy(film)
         reduce_film(t, dst=0)
+        # render_sharded called TWICE on the same accumulating film (the round-1 advisor's double-count case): waves 1-3, then 4-5
+        acc = torch.zeros((scene.height, scene.width, 4), dtype=torch.float32)
+        rr = OracleRenderer(vol)
+        render_sharded(rr, scene, acc, 1, 3, rank, world)
+        render_sharded(rr, scene, acc, 4, 2, rank, world)
+        # tile-row stripes of wave 2, gathered
+        tb, tc, y0, y1 = shard_tile_rows(scene, rank, world)
+        stripes = torch.zeros_like(acc)
+        wave2 = np.zeros_like(film)
+        vol.render(scene, wave2, first_wave=2, n_waves=1, threads=2)
+        stripes[y0:y1] = torch.from_numpy(wave2)[y0:y1]   # this rank's band only
+        gather_film_stripes(stripes, scene, rank, world)
         if rank == 0:
             full = np.zeros_like(film)
             vol.render(scene, full, first_wave=1, n_waves=scene.num_waves, threads=2)
-            np.savez(out_path, reduced=t.numpy(), full=full)
+            np.savez(out_path, reduced=t.numpy(), full=full, acc=acc.numpy(), stripes=stripes.numpy(), wave2=wave2)
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -74,3 +101,7 @@ def test_wave_sharded_render_equals_single_process(built, tmp_path):
     assert np.array_equal(reduced[..., 3], full[..., 3]) and (full[..., 3] == 5).all()
     assert np.allclose(reduced[..., :3], full[..., :3], rtol=2e-6, atol=1e-7)
     assert full[..., :3].sum() > 0
+    acc = z["acc"]
+    assert np.array_equal(acc[..., 3], full[..., 3]), "two render_sharded calls on one film must count every wave exactly once"
+    assert np.allclose(acc[..., :3], full[..., :3], rtol=2e-6, atol=1e-7)
+    assert np.array_equal(z["stripes"], z["wave2"]), "gathered tile-row stripes == the whole wave"

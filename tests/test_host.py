@@ -12,6 +12,7 @@ import ctypes as C
 import os
 import json
 import re
+import sys
 from pathlib import Path
 
 import numpy as np
@@ -29,6 +30,24 @@ def test_abi_exports_every_declared_symbol(api):
         assert hasattr(L, name), f"libvptcuda.so does not export {name}"
     assert sorted(declared) == sorted(api.EXPORTS), "api.EXPORTS out of date with include/vptc.h"
     assert b"sm_100a" in L.vptc_version()
+
+
+def test_host_library_has_no_cuda_dependency(api):
+    """libvpthost.so = the host-side helpers alone: exports them all, and maps no CUDA library (CPU-only tools load this one)."""
+    import subprocess
+    H = api.host_lib()
+    assert [s for s in api.HOST_EXPORTS if not hasattr(H, s)] == []
+    deps = subprocess.run(["ldd", str(api.HOST_LIB_PATH)], capture_output=True, text=True).stdout
+    assert "cuda" not in deps.lower() and "nccl" not in deps.lower()
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from volume_path_tracer_b200 import api, scenes\n"
+            "s, spec = scenes.small_variant('fire', (16, 16), 1, 0.1)\n"
+            "g = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)\n"
+            "maps = open('/proc/self/maps').read()\n"
+            "assert 'libvpthost.so' in maps and 'libvptcuda.so' not in maps, maps\n"
+            "print('ok')\n") % str(ROOT)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-1500:]
 
 
 def test_abi_struct_layout(api):

@@ -97,10 +97,56 @@ EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_last_render_ms", "vptc_device_volume_bytes",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
-    "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version",
+    "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_host_last_error",
+    "vptc_group_create", "vptc_group_destroy", "vptc_group_last_error", "vptc_group_size", "vptc_group_peer_mapped", "vptc_group_set_volume", "vptc_group_render",
+    "vptc_group_render_async", "vptc_group_wait", "vptc_group_last_render_ms", "vptc_group_context",
 ]
 
+HOST_EXPORTS = ["vptc_host_last_error", "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
+                "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version"]
+HOST_LIB_PATH = _PKG / "libvpthost.so"
+
 _lib = None
+_host_lib = None
+
+
+def _declare_host(L):
+    vp, sz, u32 = C.c_void_p, C.c_size_t, C.c_uint32
+    L.vptc_host_last_error.restype = C.c_char_p
+    L.vptc_version.restype = C.c_char_p
+    L.vptc_scene_from_json_file.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
+    L.vptc_scene_from_json.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
+    L.vptc_nvdb_read_grid.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp), C.POINTER(sz)]
+    L.vptc_nvdb_write_grids.argtypes = [C.c_char_p, C.POINTER(vp), sz]
+    L.vptc_free.argtypes = [vp]
+    L.vptc_free.restype = None
+    L.vptc_synth_volume.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.c_double, u32, C.POINTER(C.c_double), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]
+    L.vptc_write_png.argtypes = [C.c_char_p, vp, C.c_int64, C.c_int64]
+    L.vptc_film_save.argtypes = [C.c_char_p, C.POINTER(Scene), vp, u32]
+    L.vptc_film_load.argtypes = [C.c_char_p, C.POINTER(Scene), vp, C.POINTER(u32)]
+
+
+def host_lib() -> C.CDLL:
+    """The host-side helpers (scene JSON, .nvdb I/O, procedural volumes, PNG, film checkpoints): libvpthost.so, which has no CUDA
+    dependency — CPU-only tools (bench.py --impl reference, the oracle tests) never map the CUDA library. A development build chosen
+    with VPT_LIBVPTCUDA serves its own copies of the helpers."""
+    global _host_lib
+    if _host_lib is not None:
+        return _host_lib
+    if os.environ.get("VPT_LIBVPTCUDA"):
+        _host_lib = lib()
+        return _host_lib
+    if not HOST_LIB_PATH.exists():
+        raise ImportError(f"{HOST_LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` (make -C volume_path_tracer_b200/csrc)")
+    L = C.CDLL(str(HOST_LIB_PATH))
+    _declare_host(L)
+    _host_lib = L
+    return L
+
+
+def _check_host(rc: int):
+    if rc != 0:
+        raise VptError(rc, (host_lib().vptc_host_last_error() or b"").decode(errors="replace"))
 
 
 def lib() -> C.CDLL:
@@ -115,7 +161,6 @@ def lib() -> C.CDLL:
     vp, sz, u32, u64p = C.c_void_p, C.c_size_t, C.c_uint32, C.POINTER(C.c_uint64)
     L.vptc_last_error.restype = C.c_char_p
     L.vptc_last_error.argtypes = [vp]
-    L.vptc_version.restype = C.c_char_p
     L.vptc_create.argtypes = [C.POINTER(vp), C.c_int]
     L.vptc_destroy.argtypes = [vp]
     L.vptc_destroy.restype = None
@@ -140,16 +185,22 @@ def lib() -> C.CDLL:
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.vptc_film_to_image.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
     L.vptc_blackbody.argtypes = [vp, vp, sz, vp]
-    L.vptc_scene_from_json_file.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
-    L.vptc_scene_from_json.argtypes = [C.c_char_p, C.POINTER(Scene), C.c_char_p, sz]
-    L.vptc_nvdb_read_grid.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp), C.POINTER(sz)]
-    L.vptc_nvdb_write_grids.argtypes = [C.c_char_p, C.POINTER(vp), sz]
-    L.vptc_free.argtypes = [vp]
-    L.vptc_free.restype = None
-    L.vptc_synth_volume.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.c_double, u32, C.POINTER(C.c_double), C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]
-    L.vptc_write_png.argtypes = [C.c_char_p, vp, C.c_int64, C.c_int64]
-    L.vptc_film_save.argtypes = [C.c_char_p, C.POINTER(Scene), vp, u32]
-    L.vptc_film_load.argtypes = [C.c_char_p, C.POINTER(Scene), vp, C.POINTER(u32)]
+    _declare_host(L)
+    L.vptc_group_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
+    L.vptc_group_destroy.argtypes = [vp]
+    L.vptc_group_destroy.restype = None
+    L.vptc_group_last_error.argtypes = [vp]
+    L.vptc_group_last_error.restype = C.c_char_p
+    L.vptc_group_size.argtypes = [vp]
+    L.vptc_group_peer_mapped.argtypes = [vp]
+    L.vptc_group_set_volume.argtypes = [vp, vp, sz, vp, sz]
+    L.vptc_group_render.argtypes = [vp, C.POINTER(Scene), u32, u32, C.c_int, vp]
+    L.vptc_group_render_async.argtypes = [vp, C.POINTER(Scene), u32, u32, C.c_int]
+    L.vptc_group_wait.argtypes = [vp, vp]
+    L.vptc_group_last_render_ms.argtypes = [vp]
+    L.vptc_group_last_render_ms.restype = C.c_float
+    L.vptc_group_context.argtypes = [vp, C.c_int]
+    L.vptc_group_context.restype = vp
     _lib = L
     return L
 
@@ -173,7 +224,7 @@ class GridBuffer:
     def __del__(self):
         try:
             if getattr(self, "ptr", None):
-                lib().vptc_free(self.ptr)
+                host_lib().vptc_free(self.ptr)
                 self.ptr = None
         except Exception:  # interpreter shutdown
             pass
@@ -189,7 +240,7 @@ def synth_volume(kind: str, dims, voxel_size: float, seed: int = 1, anchor=None)
     (centre of the base for "fire"); default the world origin."""
     d, db, t, tb = C.c_void_p(), C.c_size_t(), C.c_void_p(), C.c_size_t()
     anc = (C.c_double * 3)(*[float(x) for x in anchor]) if anchor is not None else None
-    _check(lib().vptc_synth_volume(kind.encode(), (C.c_int32 * 3)(*[int(x) for x in dims]), float(voxel_size), int(seed), anc,
+    _check_host(host_lib().vptc_synth_volume(kind.encode(), (C.c_int32 * 3)(*[int(x) for x in dims]), float(voxel_size), int(seed), anc,
                                    C.byref(d), C.byref(db), C.byref(t), C.byref(tb)))
     return VolumeGrids(GridBuffer(d.value, db.value), GridBuffer(t.value, tb.value) if t.value else None)
 
@@ -206,10 +257,10 @@ class VolumeGrids:
     def read_from_file(path) -> "VolumeGrids":
         def read(name, required):
             p, n = C.c_void_p(), C.c_size_t()
-            rc = lib().vptc_nvdb_read_grid(str(path).encode(), name.encode(), C.byref(p), C.byref(n))
+            rc = host_lib().vptc_nvdb_read_grid(str(path).encode(), name.encode(), C.byref(p), C.byref(n))
             if rc != 0:
                 if required:
-                    _check(rc)
+                    _check_host(rc)
                 return None
             return GridBuffer(p.value, n.value)
         return VolumeGrids(read("density", True), read("temperature", False))
@@ -217,39 +268,39 @@ class VolumeGrids:
     def write(self, path):
         grids = [self.density] + ([self.temperature] if self.temperature else [])
         arr = (C.c_void_p * len(grids))(*[g.ptr for g in grids])
-        _check(lib().vptc_nvdb_write_grids(str(path).encode(), arr, len(grids)))
+        _check_host(host_lib().vptc_nvdb_write_grids(str(path).encode(), arr, len(grids)))
 
 
 def read_configuration(path):
     """-> (Scene, volume_path as written in the file).  src/configuration.cpp:8-22"""
     s, buf = Scene(), C.create_string_buffer(4096)
-    _check(lib().vptc_scene_from_json_file(str(path).encode(), C.byref(s), buf, 4096))
+    _check_host(host_lib().vptc_scene_from_json_file(str(path).encode(), C.byref(s), buf, 4096))
     return s, buf.value.decode()
 
 
 def scene_from_json(text: str):
     s, buf = Scene(), C.create_string_buffer(4096)
-    _check(lib().vptc_scene_from_json(text.encode(), C.byref(s), buf, 4096))
+    _check_host(host_lib().vptc_scene_from_json(text.encode(), C.byref(s), buf, 4096))
     return s, buf.value.decode()
 
 
 def write_png(path, rgb: np.ndarray):
     rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
-    _check(lib().vptc_write_png(str(path).encode(), _ptr(rgb), rgb.shape[1], rgb.shape[0]))
+    _check_host(host_lib().vptc_write_png(str(path).encode(), _ptr(rgb), rgb.shape[1], rgb.shape[0]))
 
 
 def film_save(path, scene: "Scene", film: np.ndarray, next_wave: int):
     """vptc_film_save: checkpoint of a progressive render (float4 film + the next wave to render)."""
     film = np.ascontiguousarray(film, dtype=np.float32)
     assert film.shape == (scene.height, scene.width, 4)
-    _check(lib().vptc_film_save(str(path).encode(), C.byref(scene), _ptr(film), int(next_wave)))
+    _check_host(host_lib().vptc_film_save(str(path).encode(), C.byref(scene), _ptr(film), int(next_wave)))
 
 
 def film_load(path, scene: "Scene"):
     """vptc_film_load -> (film, next_wave); raises VptError when the file is missing/truncated or belongs to another scene."""
     film = np.zeros((scene.height, scene.width, 4), np.float32)
     nxt = C.c_uint32(0)
-    _check(lib().vptc_film_load(str(path).encode(), C.byref(scene), _ptr(film), C.byref(nxt)))
+    _check_host(host_lib().vptc_film_load(str(path).encode(), C.byref(scene), _ptr(film), C.byref(nxt)))
     return film, int(nxt.value)
 
 
@@ -367,3 +418,54 @@ class Renderer:
         rgb = np.zeros(film.shape[:2] + (3,), np.uint8)
         _check(lib().vptc_film_to_image(self._ctx, _ptr(film), film.shape[1], film.shape[0], _ptr(rgb)), self._ctx)
         return rgb
+
+
+SHARD_WAVES, SHARD_TILES = 0, 1
+
+
+class Group:
+    """vptc_group: several GPUs behind one handle, driven by this one host thread (the reference's worker pool, src/main.cpp:63-87).
+    The volume is replicated, the job space sharded by waves (films summed over peer memory) or by stripes of tile rows (films gathered)."""
+
+    def __init__(self, devices):
+        devices = [int(d) for d in devices]
+        self._g = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib().vptc_group_create(C.byref(self._g), arr, len(devices)))
+        self.devices = devices
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise VptError(rc, (lib().vptc_group_last_error(self._g) or b"").decode(errors="replace"))
+
+    def close(self):
+        if self._g:
+            lib().vptc_group_destroy(self._g)
+            self._g = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def size(self) -> int: return int(lib().vptc_group_size(self._g))
+    def peer_mapped(self) -> int: return int(lib().vptc_group_peer_mapped(self._g))
+    def last_render_ms(self) -> float: return float(lib().vptc_group_last_render_ms(self._g))
+
+    def set_volume(self, grids: VolumeGrids):
+        t = grids.temperature
+        self._chk(lib().vptc_group_set_volume(self._g, grids.density.ptr, grids.density.nbytes, t.ptr if t else None, t.nbytes if t else 0))
+
+    def run(self, scene: Scene, film: np.ndarray, first_wave: int = 1, n_waves: int | None = None, sharding: int = SHARD_WAVES):
+        assert film.dtype == np.float32 and film.flags.c_contiguous and film.shape == (scene.height, scene.width, 4)
+        self._chk(lib().vptc_group_render(self._g, C.byref(scene), first_wave, scene.num_waves if n_waves is None else n_waves, sharding, _ptr(film)))
+        return film
+
+    def run_async(self, scene: Scene, first_wave: int, n_waves: int, sharding: int = SHARD_WAVES):
+        self._chk(lib().vptc_group_render_async(self._g, C.byref(scene), first_wave, n_waves, sharding))
+
+    def wait(self, film: np.ndarray):
+        assert film.dtype == np.float32 and film.flags.c_contiguous
+        self._chk(lib().vptc_group_wait(self._g, _ptr(film)))
+        return film

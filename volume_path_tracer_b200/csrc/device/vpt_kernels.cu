@@ -6,6 +6,7 @@
 // comparable with the CPU oracle draw for draw. Jobs are handed out by a device-side atomic counter
 // (the reference's m_job_idx.fetch_add, tile_provider.cpp:28); the film is accumulated with float4-wide
 // reductions in L2, which replaces the per-tile wave handshake (tile_provider.cpp:40-60).
+#include <algorithm>
 #include <cstdio>
 
 #include "vpt_device.cuh"
@@ -274,6 +275,21 @@ __global__ void vpt_blackbody_kernel(const float* __restrict__ bb, const float* 
     xyz[3 * i] = v.x; xyz[3 * i + 1] = v.y; xyz[3 * i + 2] = v.z;
 }
 
+// ---------------------------------------------------------------- multi-GPU film combine (vptc_group_wait, wave sharding)
+// dst += src[0] + ... + src[k-1], float4 per pixel. `dst` lives on this device; the sources are the OTHER devices' films, read in place through
+// peer mappings (NVLink / NVSwitch): the sum and the transfer are one pass, nothing is staged. HBM/NVLink bound, k + 2 float4 per pixel.
+__global__ void vpt_film_reduce_kernel(float4* __restrict__ dst, FilmSources src, int k, size_t n)
+{
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+        float4 a = dst[i];
+        for (int j = 0; j < k; ++j) {
+            const float4 b = __ldcs(src.p[j] + i); // streamed once: no reuse
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        dst[i] = a;
+    }
+}
+
 // ---------------------------------------------------------------- launchers
 cudaError_t upload_cie_table(const float* cie471x3, const float* lambda5_471)
 {
@@ -324,6 +340,18 @@ cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* v
 {
     if (n == 0) return cudaSuccess;
     vpt_sample_kernel<<<unsigned((n + 127) / 128), 128, 0, s>>>(G, xyz, n, values, dims, majorants);
+    return cudaGetLastError();
+}
+cudaError_t launch_film_reduce(float* dst, const float* const* srcs, int k, size_t n_pixels, cudaStream_t s)
+{
+    if (n_pixels == 0 || k <= 0) return cudaSuccess;
+    FilmSources fs{};
+    for (int j = 0; j < k && j < FILM_REDUCE_MAX_SRC; ++j) fs.p[j] = reinterpret_cast<const float4*>(srcs[j]);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned blocks = unsigned(std::min<size_t>((n_pixels + 255) / 256, size_t(sms) * 8));
+    vpt_film_reduce_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<float4*>(dst), fs, std::min(k, FILM_REDUCE_MAX_SRC), n_pixels);
     return cudaGetLastError();
 }
 cudaError_t launch_blackbody(const float* bb_table, const float* temps, size_t n, float* xyz, cudaStream_t s)

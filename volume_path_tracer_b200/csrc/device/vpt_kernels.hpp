@@ -31,6 +31,8 @@ struct RenderArgs {
     const unsigned int* ring_tail;// absolute number of ranges published so far (written by the host while the kernel runs)
     unsigned int range_begin;     // the range this launch was made for; its lanes start there
     unsigned int* host_done;      // mapped pinned, RING_SLOTS words: rid + 1 once range rid is complete (may be null)
+    unsigned int* exited;         // lanes of THIS launch that have left (zeroed before the launch); with exit_limit: a launch whose lanes have
+    unsigned int exit_limit;      // mostly gone stops carrying over into later ranges, so that the full grid queued behind it can take over
     float* trace_events;          // trace mode, optional: Logger<true> event log (worker.cpp:15-49), 8 floats per event
     unsigned long long* trace_event_count; unsigned long long trace_event_cap;
 };
@@ -43,6 +45,10 @@ int render_blocks_per_sm(int variant, bool trace, bool count);
 int render_jobs_per_block(int variant); // jobs a resident block works on at a time (grid sizing)
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
 cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);
+constexpr int FILM_REDUCE_MAX_SRC = 8;
+struct FilmSources { const float4* p[FILM_REDUCE_MAX_SRC]; };
+// dst (n_pixels float4 on the current device) += sum of k <= FILM_REDUCE_MAX_SRC source films, which may be peer-mapped memory of other devices
+cudaError_t launch_film_reduce(float* dst, const float* const* srcs, int k, size_t n_pixels, cudaStream_t s);
 cudaError_t launch_blackbody(const float* bb_table, const float* temps, size_t n, float* xyz, cudaStream_t s);
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);
 

@@ -37,7 +37,14 @@ namespace vptd {
 #ifndef VPT_SYNC_SETUP
 #define VPT_SYNC_SETUP 0
 #endif
+#ifndef VPT_SHADOW_IN_EVAL
+#define VPT_SHADOW_IN_EVAL 0 // a scatter begins its shadow ray inside EVAL instead of queueing for SETUP: one stage transition less per scatter (profiles/r02_kernel_ab.txt)
+#endif
+#ifndef VPT_DEFER_INF
+#define VPT_DEFER_INF 0 // a ray that leaves the volume only marks the pixel; the infinite light is added where the pixel is closed (no cold-state traffic in HOT)
+#endif
 enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
+enum : int { PH_NEXT_PIXEL_INF = 5 }; // NEXT_PIXEL for a path that escaped to the infinite light (VPT_DEFER_INF)
 
 template <bool TRACE, bool COUNT>
 __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_render_sched_kernel(const RenderArgs A)
@@ -94,10 +101,15 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }                                                                                          \
     } while (0)
     // the ray left the volume (iterator.next() -> nullopt): back to SETUP
+#if VPT_DEFER_INF
+#define VPT_ADD_INF_LIGHT() (sub = PH_NEXT_PIXEL_INF) /* L += infinite light happens where the pixel is closed: same single fp32 add per channel */
+#else
+#define VPT_ADD_INF_LIGHT() do { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; } while (0)
+#endif
 #define VPT_RAY_FINISHED()                                                                            \
     do {                                                                                              \
         if (shadow) sub = PH_AFTER_SHADOW;                                                            \
-        else { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; } \
+        else VPT_ADD_INF_LIGHT();                                                                     \
         stage = ST_SETUP;                                                                             \
     } while (0)
 
@@ -124,10 +136,11 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         if (run_setup && stage == ST_SETUP) {
             V3 rd = mk(0.0f, 0.0f, 1.0f); // direction of the ray to begin (unused by a shadow ray: shadow_dir)
             unsigned int depth = 0;
-            if (sub == PH_NEXT_PIXEL) {
+            if (sub == PH_NEXT_PIXEL || sub == PH_NEXT_PIXEL_INF) {
                 int x0 = CLDI(C_X0), y0 = CLDI(C_Y0), sx = CLDI(C_SX), sy = CLDI(C_SY), x = CLDI(C_X), y = CLDI(C_Y);
                 if (pixel_open) { // film(y,x) += (imaging_ratio * L, 1)   worker.cpp:203-204
-                    const V3 L = CLD3(C_L);
+                    V3 L = CLD3(C_L);
+                    if (VPT_DEFER_INF && sub == PH_NEXT_PIXEL_INF) { L.x += S.inf_light[0]; L.y += S.inf_light[1]; L.z += S.inf_light[2]; } // worker.cpp:198-200
                     if (COUNT) ++st.pixel_samples;
                     if (TRACE) {
                         const size_t slot = size_t(j) * size_t(S.tw * S.th) + size_t(y) * size_t(S.tw) + size_t(x);
@@ -158,12 +171,15 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         for (;;) {
                             j = atomicAdd(&R->counter, 1ULL);
                             if (j < __ldcg(&R->n_jobs)) break;
-                            if (rc + 1u >= *reinterpret_cast<const volatile unsigned int*>(A.ring_tail)) { stage = ST_EXIT; break; } // ring dry
+                            // ring dry — or this launch has thinned out (lanes leave whenever they find the ring momentarily dry; the survivors
+                            // must not nurse later ranges along while a full grid waits in the stream behind them)
+                            if (rc + 1u >= *reinterpret_cast<const volatile unsigned int*>(A.ring_tail) ||
+                                *reinterpret_cast<const volatile unsigned int*>(A.exited) > A.exit_limit) { stage = ST_EXIT; break; }
                             ++rc;
                             R = A.ring + (rc % RING_SLOTS);
                         }
                         cold[C_RANGE][lane_col] = rc;
-                        if (stage == ST_EXIT) { CSTI(C_SY, 0); break; }
+                        if (stage == ST_EXIT) { CSTI(C_SY, 0); atomicAdd(A.exited, 1u); break; }
                         uint64_t jid;
                         if (TRACE) jid = A.trace_jids[j];
                         else {
@@ -218,8 +234,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
 #endif
             if (stage != ST_EXIT) {
                 if (!shadow && depth >= S.max_depth) { // bounce loop out of depth: not terminated -> infinite light (:198-200)
-                    CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]);
-                    sub = PH_NEXT_PIXEL;
+                    VPT_ADD_INF_LIGHT();
                 } else {
                     bool ray_done;
                     const RayDir rdir = shadow ? shadow_dir : make_ray_dir(G, rd);
@@ -227,7 +242,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         if (ray_done) VPT_RAY_FINISHED();
                         else { stage = ST_HOT; mode = M_STEP; }
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
-                    else { CSTF(C_L, CLDF(C_L) + S.inf_light[0]); CSTF(C_L + 1, CLDF(C_L + 1) + S.inf_light[1]); CSTF(C_L + 2, CLDF(C_L + 2) + S.inf_light[2]); sub = PH_NEXT_PIXEL; }
+                    else VPT_ADD_INF_LIGHT(); // the camera / bounce ray misses the volume
                 }
             }
         }
@@ -353,8 +368,18 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         else {                               // scatter (also the fallback choice)
                             if (COUNT) ++st.scatter_events;
                             CST3(C_POS, point);
+#if VPT_SHADOW_IN_EVAL
+                            if (S.dist_light_on) { // sample_Ld (worker.cpp:59-66): the shadow ray begins right here; the lane goes straight back to HOT
+                                shadow = true; CSTF(C_TRAY, 1.0f);
+                                if (COUNT) ++st.shadow_rays;
+                                bool ray_done;
+                                sub = PH_AFTER_SHADOW; // where the lane goes if the shadow ray misses the volume (T stays 1) or is over at once
+                                if (flat_begin_ray_dir<COUNT>(m, G, cc, point, shadow_dir, ray_done, st) && !ray_done) { stage = ST_HOT; mode = M_STEP; }
+                            } else { CSTF(C_TRAY, 0.0f); sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
+#else
                             if (S.dist_light_on) sub = PH_BEGIN_SHADOW;
                             else { CSTF(C_TRAY, 0.0f); sub = PH_AFTER_SHADOW; } // sample_Ld returns 0 before any draw (:57)
+#endif
                         }
                     }
                 }
@@ -362,6 +387,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
     }
 #undef VPT_RAY_FINISHED
+#undef VPT_ADD_INF_LIGHT
 #undef VPT_EVENT
 #undef CLDF
 #undef CLDI

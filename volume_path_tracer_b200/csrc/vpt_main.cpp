@@ -61,10 +61,36 @@ int main(int argc, char* argv[])
         temperature = nullptr; temperature_bytes = 0;
     }
 
+    // Devices. VPT_DEVICES=0,1,2,... renders on several GPUs behind one vptc_group (the reference drives all its workers from main(),
+    // src/main.cpp:63-87): volume replicated, job space sharded by waves (VPT_SHARD=waves, default) or by stripes of tile rows
+    // (VPT_SHARD=tiles), films combined on the first device. VPT_DEVICE=n (or nothing) renders on one GPU.
+    std::vector<int> devices;
+    if (const char* ds = std::getenv("VPT_DEVICES")) {
+        for (const char* p = ds; *p;) {
+            char* end = nullptr;
+            const long v = std::strtol(p, &end, 10);
+            if (end == p) vptFATAL("VPT_DEVICES must be a comma-separated list of device indices");
+            devices.push_back(int(v));
+            p = *end == ',' ? end + 1 : end;
+            if (*end && *end != ',') vptFATAL("VPT_DEVICES must be a comma-separated list of device indices");
+        }
+    }
+    const char* shard_env = std::getenv("VPT_SHARD");
+    const int sharding = shard_env && std::string(shard_env) == "tiles" ? VPTC_SHARD_TILES : VPTC_SHARD_WAVES;
+    if (shard_env && std::string(shard_env) != "tiles" && std::string(shard_env) != "waves") vptFATAL("VPT_SHARD must be \"waves\" or \"tiles\"");
     const char* dev_env = std::getenv("VPT_DEVICE");
+    vptc_group* group = nullptr;
     vptc_ctx* ctx = nullptr;
-    if (vptc_create(&ctx, dev_env ? std::atoi(dev_env) : 0) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
-    if (vptc_set_volume(ctx, density, density_bytes, temperature, temperature_bytes) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+    if (devices.size() > 1) {
+        if (vptc_group_create(&group, devices.data(), int(devices.size())) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+        if (vptc_group_set_volume(group, density, density_bytes, temperature, temperature_bytes) != VPTC_OK) vptFATAL(vptc_group_last_error(group));
+        ctx = vptc_group_context(group, 0); // trace hooks and the resolve run on the first device
+        vptINFO("Rendering on " << devices.size() << " devices (" << (sharding == VPTC_SHARD_TILES ? "tile stripes, gathered" : "waves, summed") << "; "
+                << vptc_group_peer_mapped(group) << " of " << devices.size() - 1 << " peers mapped directly)");
+    } else {
+        if (vptc_create(&ctx, devices.size() == 1 ? devices[0] : (dev_env ? std::atoi(dev_env) : 0)) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+        if (vptc_set_volume(ctx, density, density_bytes, temperature, temperature_bytes) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+    }
     vptc_free(density); vptc_free(temperature); // the library baked its own copy
     if (const char* tp = std::getenv("VPT_TRACE_PIXEL")) {
         long long tx = -1, ty = -1;
@@ -128,19 +154,35 @@ int main(int argc, char* argv[])
         uint32_t n = std::min(per_call, cfg.num_waves - wave + 1);
         if (save_every) n = std::min(n, save_every - (wave - 1) % save_every); // calls end on multiples of K
         vptINFO("Starting wave " << wave << "/" << cfg.num_waves);
+        if (group) { // the devices' films keep accumulating on the devices; they are combined where the film is needed (a save, the end)
+            if (vptc_group_render_async(group, &cfg, wave, n, sharding) != VPTC_OK) vptFATAL(vptc_group_last_error(group));
+            wave += n;
+            if (save_every && (wave - 1) % save_every == 0 && wave <= cfg.num_waves) {
+                if (vptc_group_wait(group, film.data()) != VPTC_OK) vptFATAL(vptc_group_last_error(group));
+                device_ms += vptc_group_last_render_ms(group);
+                save(wave);
+            }
+            continue;
+        }
         if (vptc_render_async(ctx, &cfg, wave, n, film.data()) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
         in_film = wave; // the previous calls are in `film` now; this one is on the device
         wave += n;
         if (save_every && in_film > first_wave && (in_film - 1) % save_every == 0) save(in_film);
     }
-    if (vptc_wait(ctx) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
-    device_ms = vptc_last_render_ms(ctx);
+    if (group) {
+        if (vptc_group_wait(group, film.data()) != VPTC_OK) vptFATAL(vptc_group_last_error(group));
+        device_ms += vptc_group_last_render_ms(group);
+    } else {
+        if (vptc_wait(ctx) != VPTC_OK) vptFATAL(vptc_last_error(ctx));
+        device_ms = vptc_last_render_ms(ctx);
+    }
     if (g_stop && wave <= cfg.num_waves) vptINFO("Stopped at wave " << wave - 1 << "/" << cfg.num_waves);
     const auto elapsed = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - start);
     const double rendered = double(W) * double(H) * double(wave - first_wave);
     vptINFO("Rendering complete in " << elapsed.count() << " ms (" << device_ms << " ms on the device, "
             << (device_ms > 0.0 ? rendered / (device_ms * 1e-3) / 1e6 : 0.0) << " M pixel-samples/s)");
     save(wave);
-    vptc_destroy(ctx);
+    if (group) vptc_group_destroy(group);
+    else vptc_destroy(ctx);
     return 0;
 }

@@ -53,7 +53,7 @@ struct vptc_ctx {
     // ---- range ring (device/layout.hpp RangeDesc): every render call of the default kernel is published here ----
     cudaStream_t ctl = nullptr;      // non-blocking stream: ring publication, film zeroing and staging copies run BESIDE the render kernel
     cudaEvent_t ev_ctl = nullptr;
-    RangeDesc* d_ring = nullptr; unsigned int* d_tail = nullptr;
+    RangeDesc* d_ring = nullptr; unsigned int* d_tail = nullptr; unsigned int* d_exited = nullptr;
     RangeDesc* h_ring = nullptr; unsigned int* h_tail = nullptr; // pinned staging, one slot per ring slot
     unsigned int* h_done = nullptr; unsigned int* d_done = nullptr; // mapped pinned completion flags (host pointer / device alias)
     unsigned int n_ranges = 0;       // ranges published so far (absolute range number of the next one)
@@ -64,6 +64,8 @@ struct vptc_ctx {
     // host-film path: two device films + pinned staging; at most one call's film is still on the device
     float* film[2] = {nullptr, nullptr}; size_t film_floats = 0;
     float* pinned = nullptr; size_t pinned_floats = 0;
+    float* pinned_zero = nullptr;    // as large as a film, all zero: films are cleared by an H2D COPY (copy engine), because a memset is a kernel
+                                     // and would wait behind the persistent render kernel that fills every SM
     struct Pending { bool active = false; unsigned int rid = 0; float* host_film = nullptr; size_t n = 0; int buf = 0; } pending;
     int next_buf = 0;
     cudaEvent_t ev_launch[2] = {nullptr, nullptr}; // after the kernel launched for the call using film[b]
@@ -188,17 +190,24 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
     const unsigned long long per_block = (unsigned long long)(render_jobs_per_block(variant));
     const unsigned long long want = (r.n_jobs + per_block - 1) / per_block, full = (unsigned long long)(ctx->num_sms) * per_sm;
     const int blocks = int(full_grid ? full : std::min<unsigned long long>(want ? want : 1ULL, full));
+    A.exited = ctx->d_exited; A.exit_limit = unsigned(blocks) * unsigned(per_block) / 2u;
+    CU(cudaMemsetAsync(ctx->d_exited, 0, sizeof(unsigned int), ctx->stream)); // same stream: runs between the previous launch and this one
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     CU(launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     return VPTC_OK;
 }
 
+int read_counters(vptc_ctx* ctx);
 // Wait for the launch enqueue_render made; fills last_ms / counters.
 int finish_render(vptc_ctx* ctx)
 {
     CU(cudaEventSynchronize(ctx->ev1));
     CU(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
+    return read_counters(ctx);
+}
+int read_counters(vptc_ctx* ctx)
+{
     if (ctx->count) {
         CountersDev h;
         CU(cudaMemcpy(&h, ctx->counters, sizeof(h), cudaMemcpyDeviceToHost));
@@ -244,7 +253,7 @@ int collect_pending(vptc_ctx* ctx)
     ctx->pending.active = false;
     const unsigned int slot = p.rid % RING_SLOTS;
     for (unsigned spin = 0;; ++spin) {
-        if (*reinterpret_cast<volatile unsigned int*>(ctx->h_done + slot) == p.rid + 1u) break;
+        if (p.rid != ~0u && *reinterpret_cast<volatile unsigned int*>(ctx->h_done + slot) == p.rid + 1u) break;
         const cudaError_t q = cudaEventQuery(ctx->ev_launch[p.buf]);
         if (q == cudaSuccess) break; // the kernel launched for this range has exited: the range is complete
         if (q != cudaErrorNotReady) return fail(ctx, VPTC_ERR_CUDA, std::string("render kernel failed: ") + cudaGetErrorString(q));
@@ -265,12 +274,13 @@ int wait_all(vptc_ctx* ctx)
         cudaError_t e = cudaEventSynchronize(ctx->ev1);
         if (e == cudaSuccess) e = cudaEventElapsedTime(&ctx->last_ms, ctx->ev_series, ctx->ev1);
         if (e != cudaSuccess && rc == VPTC_OK) rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_wait: ") + cudaGetErrorString(e));
+        if (rc == VPTC_OK) rc = read_counters(ctx);
     }
     return rc;
 }
 
 // Common front of the asynchronous render calls: argument checks, joins (or opens) the series, enqueues one launch for the range.
-int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* jr, float* d_film, unsigned int* rid)
+int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* jr, float* d_film, unsigned int* rid, bool* launched = nullptr)
 {
     if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
     if (int rc = check_scene(ctx, scene)) return rc;
@@ -286,7 +296,9 @@ int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* 
     r.tile_begin = jr->tile_begin; r.tile_count = jr->tile_count ? jr->tile_count : sd.ntiles;
     if (r.tile_begin > sd.ntiles || r.tile_count > sd.ntiles - r.tile_begin) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "render: tile range outside the frame's tiles");
     r.n_jobs = r.tile_count * (unsigned long long)jr->n_waves;
-    if (r.n_jobs == 0) { if (rid) *rid = ~0u; return VPTC_OK; }
+    if (launched) *launched = false;
+    if (rid) *rid = ~0u; // stays ~0 for the kernels that do not read the ring (variants 0, 1, 3)
+    if (r.n_jobs == 0) return VPTC_OK;
     if (!ctx->series_open) {
         CU(cudaEventRecord(ctx->ev_series, ctx->stream));
         std::memset(&ctx->series_scene, 0, sizeof(SceneDev)); // padding bytes take part in the memcmp above
@@ -297,8 +309,43 @@ int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* 
     if (int rc = enqueue_render(ctx, scene, A, r, /*trace=*/false, /*full_grid=*/joinable, &id)) return rc;
     ctx->series_open = true; ++ctx->series_launches;
     if (rid) *rid = id;
+    if (launched) *launched = true;
     return VPTC_OK;
 }
+// fix_majorants_for_interpolation + the brick layout, on the host (csrc/host/bake.cpp). A corrupt buffer is VPTC_ERR_BAD_GRID.
+int bake_volume(vptc_ctx* ctx, const void* density_grid, size_t density_bytes, const void* temperature_grid, size_t temperature_bytes,
+                vpt_host::BakedGrid& b, vpt_host::BakedGrid& t, bool& has_temperature)
+{
+    has_temperature = false;
+    try {
+        vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
+        if (temperature_grid && temperature_bytes) {
+            vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t);
+            has_temperature = true;
+        }
+    } catch (const std::exception& e) {
+        return fail(ctx, VPTC_ERR_BAD_GRID, std::string("vptc_set_volume: ") + e.what());
+    }
+    return VPTC_OK;
+}
+
+// Stage baked grids into FRESH device grids and swap only when everything succeeded: a failed call (out of device memory on a larger
+// second volume) leaves the context rendering the previous volume, never a half-released one.
+int stage_volume(vptc_ctx* ctx, const vpt_host::BakedGrid& b, const vpt_host::BakedGrid* t)
+{
+    CU(cudaSetDevice(ctx->device));
+    if (int rc = wait_all(ctx)) return rc; // nothing may still be rendering the volume about to be replaced
+    CU(cudaStreamSynchronize(ctx->stream));
+    DeviceGrid new_density, new_temperature;
+    if (int rc = upload(ctx, b, new_density)) return rc;
+    if (t) if (int rc = upload(ctx, *t, new_temperature)) { new_density.release(); return rc; }
+    ctx->density.release(); ctx->temperature.release();
+    ctx->density = new_density; ctx->temperature = new_temperature;
+    ctx->has_temperature = t != nullptr;
+    ctx->has_volume = true;
+    return VPTC_OK;
+}
+
 } // namespace
 
 extern "C" {
@@ -335,6 +382,7 @@ int vptc_create(vptc_ctx** out, int device)
     for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&ctx->ev_launch[b], cudaEventDisableTiming));
     CU(cudaMalloc(&ctx->d_ring, sizeof(RangeDesc) * RING_SLOTS));
     CU(cudaMemset(ctx->d_ring, 0, sizeof(RangeDesc) * RING_SLOTS));
+    CU(cudaMalloc(&ctx->d_exited, sizeof(unsigned int)));
     CU(cudaMalloc(&ctx->d_tail, sizeof(unsigned int)));
     CU(cudaMemset(ctx->d_tail, 0, sizeof(unsigned int)));
     CU(cudaMallocHost(&ctx->h_ring, sizeof(RangeDesc) * RING_SLOTS));
@@ -365,8 +413,9 @@ void vptc_destroy(vptc_ctx* ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->ctl) cudaStreamSynchronize(ctx->ctl);
     cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film[0]); cudaFree(ctx->film[1]);
-    cudaFree(ctx->d_ring); cudaFree(ctx->d_tail);
+    cudaFree(ctx->d_ring); cudaFree(ctx->d_tail); cudaFree(ctx->d_exited);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->pinned_zero) cudaFreeHost(ctx->pinned_zero);
     if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
     if (ctx->h_tail) cudaFreeHost(ctx->h_tail);
     if (ctx->h_done) cudaFreeHost(ctx->h_done);
@@ -384,34 +433,10 @@ int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_byte
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: ctx is null");
     if (!density_grid) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_set_volume: the density grid is required (volume_grids.cpp:48-56)");
-    CU(cudaSetDevice(ctx->device));
-    if (int rc = wait_all(ctx)) return rc; // nothing may still be rendering the volume about to be replaced
-    CU(cudaStreamSynchronize(ctx->stream));
-    // Stage into fresh device grids and swap only when EVERYTHING succeeded: a failed call (corrupt buffer, out of device memory on a
-    // larger second volume) leaves the context rendering the previous volume, never a half-released one.
-    DeviceGrid new_density, new_temperature;
-    bool new_has_temperature = false;
-    try {
-        {
-            vpt_host::BakedGrid b;
-            vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
-            if (int rc = upload(ctx, b, new_density)) return rc;
-        }
-        if (temperature_grid && temperature_bytes) {
-            vpt_host::BakedGrid t;
-            vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t);
-            if (int rc = upload(ctx, t, new_temperature)) { new_density.release(); return rc; }
-            new_has_temperature = true;
-        }
-    } catch (const std::exception& e) {
-        new_density.release(); new_temperature.release();
-        return fail(ctx, VPTC_ERR_BAD_GRID, std::string("vptc_set_volume: ") + e.what());
-    }
-    ctx->density.release(); ctx->temperature.release();
-    ctx->density = new_density; ctx->temperature = new_temperature;
-    ctx->has_temperature = new_has_temperature;
-    ctx->has_volume = true;
-    return VPTC_OK;
+    vpt_host::BakedGrid b, t;
+    bool has_t = false;
+    if (int rc = bake_volume(ctx, density_grid, density_bytes, temperature_grid, temperature_bytes, b, t, has_t)) return rc;
+    return stage_volume(ctx, b, has_t ? &t : nullptr);
 }
 
 int vptc_wait(vptc_ctx* ctx)
@@ -459,20 +484,26 @@ int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wav
         for (int b = 0; b < 2; ++b) { cudaFree(ctx->film[b]); ctx->film[b] = nullptr; }
         ctx->film_floats = 0;
         if (ctx->pinned) cudaFreeHost(ctx->pinned);
-        ctx->pinned = nullptr; ctx->pinned_floats = 0;
+        if (ctx->pinned_zero) cudaFreeHost(ctx->pinned_zero);
+        ctx->pinned = ctx->pinned_zero = nullptr; ctx->pinned_floats = 0;
         for (int b = 0; b < 2; ++b) CU(cudaMalloc(&ctx->film[b], n * sizeof(float)));
         ctx->film_floats = n;
         CU(cudaMallocHost(&ctx->pinned, n * sizeof(float)));
+        CU(cudaMallocHost(&ctx->pinned_zero, n * sizeof(float)));
+        std::memset(ctx->pinned_zero, 0, n * sizeof(float));
         ctx->pinned_floats = n;
     }
     // The device renders this call's waves into a zeroed film of its own; the host later ADDS it into the caller's film, which keeps the
     // reference's "film accumulates" contract without uploading the old film. Buffer b was last used two calls ago and has been collected.
     const int b = ctx->next_buf;
-    CU(cudaMemsetAsync(ctx->film[b], 0, n * sizeof(float), ctx->ctl)); // ordered before the range is published (same stream)
+    CU(cudaMemcpyAsync(ctx->film[b], ctx->pinned_zero, n * sizeof(float), cudaMemcpyHostToDevice, ctx->ctl)); // cleared before the range is published (same stream)
+    CU(cudaEventRecord(ctx->ev_ctl, ctx->ctl));
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_ctl, 0)); // kernels that do not read the ring (variants 0, 1, 3) are ordered after the clear by this
     const vptc_job_range jr{first_wave, n_waves, 1, 0, 0, 0};
     unsigned int rid = ~0u;
-    if (int rc = enqueue_async(ctx, scene, &jr, ctx->film[b], &rid)) return rc;
-    if (rid == ~0u) return VPTC_OK; // nothing to render
+    bool launched = false;
+    if (int rc = enqueue_async(ctx, scene, &jr, ctx->film[b], &rid, &launched)) return rc;
+    if (!launched) return VPTC_OK; // nothing to render
     CU(cudaEventRecord(ctx->ev_launch[b], ctx->stream));
     // now that the GPU has this call's work, bring home the previous call's film (its range completes while this one is already running)
     const int rc = collect_pending(ctx);
@@ -731,5 +762,7 @@ int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int
     if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image: ") + cudaGetErrorString(e));
     return VPTC_OK;
 }
+
+#include "vptc_group_impl.hpp" // vptc_group_*: several devices behind one handle (same translation unit: it drives the contexts' internals)
 
 } // extern "C"

@@ -34,6 +34,8 @@ void* dup_aligned(const std::vector<uint8_t>& v)
 
 extern "C" {
 
+const char* vptc_host_last_error(void) { return vptc_internal::global_error(); }
+
 const char* vptc_version(void) { return "vpt-b200 0.1 (sm_100a)"; }
 
 void vptc_free(void* p) { std::free(p); }

@@ -27,12 +27,16 @@ def shard_waves(first_wave: int, n_waves: int, rank: int, world: int) -> Tuple[i
     return first_wave + rank, count, world
 
 
-def shard_tiles(ntiles: int, rank: int, world: int) -> Tuple[int, int]:
-    """Contiguous tile-stripe partition [begin, end) — the low-spp alternative (disjoint pixels, gather instead of
-    reduce). Kept for completeness of §8e; the wave sharding above is what render_sharded uses."""
-    base, rem = divmod(ntiles, world)
-    begin = rank * base + min(rank, rem)
-    return begin, begin + base + (1 if rank < rem else 0)
+def shard_tile_rows(scene, rank: int, world: int) -> Tuple[int, int, int, int]:
+    """Tile-stripe partition for low spp / large frames (the reference numbers tiles row-major, src/tile_provider.cpp:95-105): rank r
+    takes a contiguous block of tile ROWS, i.e. one contiguous band of film rows. -> (tile_begin, tile_count, y0, y1) for
+    vptc_job_range / Renderer.run_device_range; disjoint pixels across ranks, so the films are GATHERED, not summed."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    W, H, tw, th = scene.width, scene.height, int(scene.tile_size[0]), int(scene.tile_size[1])
+    ntx, nty = -(-W // tw), -(-H // th)
+    r0, r1 = nty * rank // world, nty * (rank + 1) // world
+    return r0 * ntx, (r1 - r0) * ntx, min(H, r0 * th), min(H, r1 * th)
 
 
 def reduce_film(film, dst: int = 0):
@@ -43,12 +47,42 @@ def reduce_film(film, dst: int = 0):
     return film
 
 
-def render_sharded(renderer, scene, d_film, first_wave: int, n_waves: int, rank: int, world: int, reduce: bool = True):
-    """Render this rank's waves of [first_wave, first_wave + n_waves) into the device film tensor `d_film`
-    (H, W, 4 float32 on the renderer's device, accumulated into), then reduce onto rank 0."""
+def gather_film_stripes(film, scene, rank: int, world: int, dst: int = 0):
+    """Tile-stripe sharding: every rank's band of film rows (shard_tile_rows) is gathered into rank `dst`'s film with ONE collective
+    (NCCL gather over NVLink on GPUs, gloo in the CPU tests). Bands differ by at most one tile row: padded to the tallest for the call."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return film
+    bands = [shard_tile_rows(scene, r, world)[2:] for r in range(world)]
+    rows = max(y1 - y0 for y0, y1 in bands)
+    y0, y1 = bands[rank]
+    send = torch.zeros((rows,) + tuple(film.shape[1:]), dtype=film.dtype, device=film.device)
+    send[: y1 - y0] = film[y0:y1]
+    recv = [torch.empty_like(send) for _ in range(world)] if rank == dst else None
+    dist.gather(send, recv, dst=dst)
+    if rank == dst:
+        for r, (a, b) in enumerate(bands):
+            if r != dst and b > a:
+                film[a:b] = recv[r][: b - a]
+    return film
+
+
+def render_sharded(renderer, scene, d_film, first_wave: int, n_waves: int, rank: int, world: int, reduce: bool = True, scratch=None):
+    """Render this rank's waves of [first_wave, first_wave + n_waves) and accumulate the COMBINED result into rank 0's `d_film`
+    (H, W, 4 float32 on the renderer's device). The reduce runs on a per-call partial film (`scratch`, allocated when not given), never on
+    the accumulated one: reducing `d_film` itself would re-add every earlier call's contribution of the other ranks on the second call."""
+    import torch
     first, count, stride = shard_waves(first_wave, n_waves, rank, world)
+    if world == 1 or not reduce:
+        if count:
+            renderer.run_device(scene, d_film.data_ptr(), first, count, stride)
+        return d_film
+    part = scratch if scratch is not None else torch.empty_like(d_film)
+    part.zero_()
     if count:
-        renderer.run_device(scene, d_film.data_ptr(), first, count, stride)
-    if reduce:
-        reduce_film(d_film)
+        renderer.run_device(scene, part.data_ptr(), first, count, stride)
+    reduce_film(part)
+    if rank == 0:
+        d_film.add_(part)
     return d_film
