@@ -375,6 +375,7 @@ def run_ours(args):
     t0 = time.time()
     r.set_volume(grids)
     bake_s = time.time() - t0
+    device_volume_mb = round(r.device_volume_bytes() / 1e6, 1)
     d_film = torch.zeros((H, W, 4), dtype=torch.float32, device=dev)           # the accumulated film (meaningful on rank 0)
     d_step = torch.zeros_like(d_film) if world > 1 else None                     # this step's partial film, reduced onto rank 0
 
@@ -515,7 +516,7 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, scene, spec, grids),
             "run": {"parallelism": f"wave-sharded x{world}, volume replicated, 1 NCCL film reduce per step" if world > 1 else "single GPU",
-                    "device_volume_mb": round(r.device_volume_bytes() / 1e6, 1), "synth_s": round(synth_s, 2), "bake_upload_s": round(bake_s, 2),
+                    "device_volume_mb": device_volume_mb, "synth_s": round(synth_s, 2), "bake_upload_s": round(bake_s, 2),
                     "timed_sample_counts_exact": counts_ok},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 200 + W * H * 16, "d2h_bytes_per_step": W * H * 16,
                     "note": "vptc_render: scene POD (200 B) in, this call's device film cleared by a copy-engine upload of zeros, float4 film out and accumulated "

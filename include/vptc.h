@@ -142,6 +142,19 @@ VPTC_API int vptc_render_device_async(vptc_ctx* ctx, const vptc_scene* scene, co
 VPTC_API int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, float* film_xyzw);
 VPTC_API int vptc_wait(vptc_ctx* ctx);
 
+/* Variance-driven adaptive wave count. The reference renders every tile for num_waves waves and can only be stopped as a
+ * whole (TileProvider::stop_at_next_wave, src/tile_provider.cpp:107-111); here each TILE stops on its own once the relative standard error of
+ * its mean luminance (Y of the XYZ film) falls to rel_error: waves are rendered in batches of batch_waves, and after a batch a tile leaves the
+ * job space when  sqrt(mean over its pixels of s^2/n) / (mean over its pixels of y-bar) <= rel_error  (s^2 = unbiased sample variance of a
+ * pixel's n luminance samples, kept in a second-moment plane beside the film), never before min_waves and never after max_waves.
+ * Job ids are unchanged, so a tile's film is exactly the plain render truncated at the wave the tile stopped: film.w holds each pixel's sample
+ * count, film.xyz the sums (ADDED into film_xyzw like vptc_render). rel_error = 0 never stops: the plain render plus its second moments.
+ * Outside the bit-exact contract by construction (the reference has no such mode): validated against the CPU oracle by Monte-Carlo statistics.
+ * sum_y2 (H*W floats, ADDED into; may be NULL) receives sum of (imaging_ratio*L.y)^2 per pixel; tile_waves (ntiles, may be NULL) the waves per tile. */
+typedef struct vptc_adaptive_params { uint32_t max_waves, batch_waves, min_waves; float rel_error; } vptc_adaptive_params;
+VPTC_API int vptc_render_adaptive(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, const vptc_adaptive_params* params,
+                                  float* film_xyzw, float* sum_y2, uint32_t* tile_waves);
+
 /* ---- several GPUs behind one handle ----
  * Replaces the reference's worker pool as a whole: src/main.cpp:63-87 spawns num_workers threads that share ONE TileProvider, ONE Volume and
  * ONE film. A group is that, with GPUs for workers: one host thread drives every listed device, the baked volume is replicated in each

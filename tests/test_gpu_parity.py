@@ -575,3 +575,61 @@ def test_device_async_series_and_tile_stripes(renderer, loaded):
     assert torch.equal(series[..., 3], ref[..., 3]) and torch.allclose(series, ref, rtol=1e-5, atol=1e-7)
     with pytest.raises(Exception):
         renderer.run_device_range(scene, series.data_ptr(), 1, 1, 1, tile_begin=nt - 1, tile_count=5)
+
+
+# ---------------------------------------------------------------- adaptive wave count
+def test_adaptive_render_contract(renderer, loaded):
+    """vptc_render_adaptive: rel_error 0 is the plain render plus second moments; a huge rel_error stops every tile after the first eligible
+    batch; in between, a tile's film is the plain render truncated at the wave the tile stopped (job ids are unchanged)."""
+    scene, spec, grids = loaded("fire")
+    ntx = -(-scene.width // int(scene.tile_size[0]))
+    # one wave, never stopping: the film is the plain wave, and sum_y2 is exactly the square of the one luminance sample
+    f1, sq1, tw1 = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=1, batch_waves=1, rel_error=0.0)
+    plain1 = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=1)
+    assert np.array_equal(f1, plain1) and (tw1 == 1).all()
+    assert np.array_equal(sq1, plain1[..., 1] * plain1[..., 1])
+    # never stopping, many waves
+    f, sq, tw = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=24, batch_waves=8, rel_error=0.0)
+    plain = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=24)
+    assert (tw == 24).all() and np.array_equal(f[..., 3], plain[..., 3]) and np.allclose(f, plain, rtol=1e-5, atol=1e-7)
+    n = f[..., 3]
+    var = (sq - f[..., 1] ** 2 / n) / (n - 1)
+    assert (var > -1e-6 * np.maximum(sq / n, 1e-30)).all(), "second moments must dominate the squared mean"
+    # everything stops at the first eligible batch
+    f, sq, tw = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=64, batch_waves=4, rel_error=1e9, min_waves=8)
+    assert (tw == 8).all() and (f[..., 3] == 8).all()
+    # a real threshold: per-pixel counts are the tile's wave count, tiles differ, and each tile is the truncated plain render
+    f, sq, tw = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=96, batch_waves=8, rel_error=0.06, min_waves=8)
+    th, twid = int(scene.tile_size[1]), int(scene.tile_size[0])
+    per_pixel = np.repeat(np.repeat(tw.reshape(-1, ntx), th, axis=0), twid, axis=1)[: scene.height, : scene.width]
+    assert np.array_equal(f[..., 3], per_pixel.astype(np.float32))
+    assert tw.min() == 8 and tw.max() > tw.min() and (tw % 8 == 0).all(), "noise-free sky tiles stop at once, the flame keeps going"
+    for w in np.unique(tw)[:3]:
+        ref = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=int(w))
+        m = per_pixel == w
+        assert np.allclose(f[m], ref[m], rtol=1e-5, atol=1e-7)
+    saved = 1.0 - tw.astype(np.float64).sum() / (96.0 * len(tw))
+    print(f"\n[adaptive fire 70x100, rel_error 0.06] waves per tile min {tw.min()} / mean {tw.mean():.1f} / max {tw.max()}: {100 * saved:.0f} % of the 96-wave work skipped")
+
+
+def test_adaptive_image_within_monte_carlo_noise(renderer, oracle, loaded):
+    """The adaptive film's per-pixel mean against an independent CPU-oracle render: inside 3 sigma of the combined Monte-Carlo noise (sigma from
+    the GPU's own second-moment plane), at the rate a plain GPU render achieves against the same CPU render."""
+    scene, spec, grids = loaded("fire")
+    f, sq, tw = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=256, batch_waves=16, rel_error=0.03, min_waves=16)
+    cpu = np.zeros((scene.height, scene.width, 4), np.float32)
+    n_c = 48
+    oracle.volume(grids).render(scene, cpu, first_wave=1001, n_waves=n_c)  # independent waves
+    plain = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=256)
+    _, sq_p, _ = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=256, batch_waves=256, rel_error=0.0)
+
+    def inside(film, sq2):
+        n = film[..., 3].astype(np.float64)
+        m = film[..., 1] / n
+        var = np.maximum(sq2 / n - m * m, 0) * n / np.maximum(n - 1, 1)
+        d = m - cpu[..., 1] / n_c
+        tol = 3.0 * np.sqrt(var * (1.0 / n + 1.0 / n_c)) + 1e-7
+        return float((np.abs(d) <= tol).mean())
+    got, control = inside(f, sq), inside(plain, sq_p)
+    print(f"\n[adaptive vs CPU oracle, fire 70x100] inside 3 sigma: adaptive {got:.4f}, plain 256-wave control {control:.4f}; mean waves/tile {tw.mean():.1f} of 256")
+    assert got > 0.985 and got > control - 0.01

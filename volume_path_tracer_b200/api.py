@@ -87,6 +87,11 @@ class JobRange(C.Structure):
                 ("tile_begin", C.c_uint64), ("tile_count", C.c_uint64)]
 
 
+class AdaptiveParams(C.Structure):
+    """vptc_adaptive_params"""
+    _fields_ = [("max_waves", C.c_uint32), ("batch_waves", C.c_uint32), ("min_waves", C.c_uint32), ("rel_error", C.c_float)]
+
+
 class VptError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"vptc error {code}: {msg}")
@@ -94,7 +99,7 @@ class VptError(RuntimeError):
 
 
 EXPORTS = [
-    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_last_render_ms", "vptc_device_volume_bytes",
+    "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_render_adaptive", "vptc_last_render_ms", "vptc_device_volume_bytes",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_host_last_error",
@@ -171,6 +176,7 @@ def lib() -> C.CDLL:
     L.vptc_render_device_async.argtypes = [vp, C.POINTER(Scene), C.POINTER(JobRange), vp]
     L.vptc_render_async.argtypes = [vp, C.POINTER(Scene), u32, u32, vp]
     L.vptc_wait.argtypes = [vp]
+    L.vptc_render_adaptive.argtypes = [vp, C.POINTER(Scene), u32, C.POINTER(AdaptiveParams), vp, vp, vp]
     L.vptc_last_render_ms.argtypes = [vp]
     L.vptc_last_render_ms.restype = C.c_float
     L.vptc_device_volume_bytes.argtypes = [vp]
@@ -373,6 +379,15 @@ class Renderer:
 
     def wait(self):
         _check(lib().vptc_wait(self._ctx), self._ctx)
+
+    def run_adaptive(self, scene: Scene, film: np.ndarray, max_waves: int, batch_waves: int, rel_error: float, min_waves: int = 0, first_wave: int = 1):
+        """vptc_render_adaptive -> (film, sum_y2 (H, W), waves per tile): each tile stops when its relative standard error <= rel_error."""
+        assert film.dtype == np.float32 and film.flags.c_contiguous and film.shape == (scene.height, scene.width, 4)
+        sq = np.zeros((scene.height, scene.width), np.float32)
+        tw = np.zeros(scene.ntiles, np.uint32)
+        p = AdaptiveParams(max_waves, batch_waves, min_waves, rel_error)
+        _check(lib().vptc_render_adaptive(self._ctx, C.byref(scene), first_wave, C.byref(p), _ptr(film), _ptr(sq), _ptr(tw)), self._ctx)
+        return film, sq, tw
 
     def trace_jobs(self, scene: Scene, jids):
         jids = np.ascontiguousarray(jids, dtype=np.uint64)

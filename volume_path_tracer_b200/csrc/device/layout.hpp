@@ -74,7 +74,7 @@ struct SceneDev {
 // cover only a stripe of tiles [tile_begin, tile_begin + tile_count) (multi-GPU tile sharding, src/tile_provider.cpp:95-105).
 //   job j of the range:  k = j / tile_count,  tile = tile_begin + j % tile_count,  jid = (first_wave - 1 + k * wave_stride) * ntiles + tile
 constexpr unsigned RING_SLOTS = 64;
-struct RangeDesc { // 64 bytes
+struct RangeDesc { // 80 bytes
     unsigned long long counter;  // next job index of the range = TileProvider::m_job_idx (tile_provider.cpp:28); device atomics only
     unsigned long long done;     // jobs finished; the lane that makes it n_jobs raises host_done[slot]
     unsigned long long n_jobs;   // tile_count * n_waves
@@ -82,8 +82,11 @@ struct RangeDesc { // 64 bytes
     unsigned long long tile_begin, tile_count;
     uint32_t first_wave, wave_stride;
     uint32_t rid, pad_;          // absolute range number (slot = rid % RING_SLOTS)
+    // statistics launches only (the STATS instantiation of the kernel; adaptive rendering):
+    const uint32_t* tile_list;   // when set: the range covers tile_list[0 .. tile_count) instead of a contiguous stripe
+    float* sum_y2;               // when set: H*W floats, += (imaging_ratio * L.y)^2 per pixel-sample (second moment of the luminance)
 };
-static_assert(sizeof(RangeDesc) == 64, "RangeDesc");
+static_assert(sizeof(RangeDesc) == 80, "RangeDesc");
 
 struct CountersDev {
     unsigned long long pixel_samples, density_evals, temperature_evals, majorant_fetches, rng_draws, scatter_events, shadow_rays;

@@ -305,6 +305,52 @@ static void launch_variant(const RenderArgs& args, int variant, int grid_blocks,
     else if (variant == 2) vpt_render_sched_kernel<TRACE, COUNT><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
     else vpt_render_pool_kernel<TRACE, COUNT><<<grid_blocks, POOL_THREADS, pool_smem_bytes<TRACE, COUNT>(), stream>>>(args);
 }
+cudaError_t launch_render_stats(const RenderArgs& args, int grid_blocks, cudaStream_t stream) // the STATS instantiation of the default kernel
+{
+    vpt_render_sched_kernel<false, false, true><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+int render_stats_blocks_per_sm()
+{
+    int n = 0;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<false, false, true>, VPT_BLOCK_THREADS, 0) == cudaSuccess ? n : 0;
+}
+// Adaptive rendering: per-tile relative standard error of the mean luminance from the film (sum y in .y, count in .w) and the second-moment
+// plane: err[t] = sqrt(mean over the tile's pixels of s^2 / n) / (mean over the pixels of y-bar), s^2 the unbiased sample variance.
+// One block per tile; tiles clipped at the frame edge use their own pixel count.
+__global__ void vpt_tile_error_kernel(const float4* film, const float* sum_y2, long long W, long long H, long long tw, long long th, long long ntx, unsigned long long ntiles, float* err)
+{
+    const unsigned long long t = blockIdx.x;
+    if (t >= ntiles) return;
+    const long long x0 = (long long)(t % (unsigned long long)ntx) * tw, y0 = (long long)(t / (unsigned long long)ntx) * th;
+    const long long sx = min(W - x0, tw), sy = min(H - y0, th);
+    double se2 = 0.0, mean = 0.0;
+    for (long long i = threadIdx.x; i < sx * sy; i += blockDim.x) {
+        const size_t p = size_t(y0 + i / sx) * size_t(W) + size_t(x0 + i % sx);
+        const float4 f = film[p];
+        const double n = f.w, m = n > 0.0 ? f.y / n : 0.0;
+        const double var = n > 1.0 ? fmax(0.0, (double(sum_y2[p]) - n * m * m) / (n - 1.0)) : 1e30; // fewer than 2 samples: not converged
+        se2 += n > 0.0 ? var / n : 1e30;
+        mean += m;
+    }
+    __shared__ double s_a[128], s_b[128];
+    s_a[threadIdx.x] = se2; s_b[threadIdx.x] = mean;
+    __syncthreads();
+    for (int k = blockDim.x / 2; k > 0; k >>= 1) {
+        if (int(threadIdx.x) < k) { s_a[threadIdx.x] += s_a[threadIdx.x + k]; s_b[threadIdx.x] += s_b[threadIdx.x + k]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double npx = double(sx * sy), rms_se = sqrt(s_a[0] / npx), mu = s_b[0] / npx;
+        err[t] = mu > 0.0 ? float(fmin(rms_se / mu, 1e30)) : (rms_se > 0.0 ? 1e30f : 0.0f); // a black, noise-free tile is converged
+    }
+}
+cudaError_t launch_tile_error(const float* film, const float* sum_y2, long long W, long long H, long long tw, long long th, long long ntx, unsigned long long ntiles, float* err, cudaStream_t s)
+{
+    if (ntiles == 0) return cudaSuccess;
+    vpt_tile_error_kernel<<<unsigned(ntiles), 128, 0, s>>>(reinterpret_cast<const float4*>(film), sum_y2, W, H, tw, th, ntx, ntiles, err);
+    return cudaGetLastError();
+}
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream)
 {
     if (trace) { if (count) launch_variant<true, true>(args, variant, grid_blocks, stream); else launch_variant<true, false>(args, variant, grid_blocks, stream); }

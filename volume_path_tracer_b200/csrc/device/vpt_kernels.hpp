@@ -42,6 +42,9 @@ cudaError_t upload_cie_table(const float* cie471x3, const float* lambda5_471); /
 //          3 = per-warp job pool in shared memory (more jobs than lanes, stage queues compacted onto lanes)
 cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool count, int grid_blocks, cudaStream_t stream);
 int render_blocks_per_sm(int variant, bool trace, bool count);
+cudaError_t launch_render_stats(const RenderArgs& args, int grid_blocks, cudaStream_t stream); // default kernel + tile lists + second-moment plane (adaptive rendering)
+int render_stats_blocks_per_sm();
+cudaError_t launch_tile_error(const float* film, const float* sum_y2, long long W, long long H, long long tw, long long th, long long ntx, unsigned long long ntiles, float* err, cudaStream_t s);
 int render_jobs_per_block(int variant); // jobs a resident block works on at a time (grid sizing)
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);
 cudaError_t launch_sample(const GridDev& G, const float* xyz, size_t n, float* values, uint32_t* dims, float* majorants, cudaStream_t s);

@@ -46,7 +46,10 @@ namespace vptd {
 enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
 enum : int { PH_NEXT_PIXEL_INF = 5 }; // NEXT_PIXEL for a path that escaped to the infinite light (VPT_DEFER_INF)
 
-template <bool TRACE, bool COUNT>
+// STATS: the instantiation adaptive rendering launches — an explicit tile list per range and a second-moment plane beside the film. A template
+// parameter, not a run-time test, so that the production instantiation's SASS does not change (the job fetch is where one extra conditional
+// load once cost 25 %: profiles/r01_codegen_cliff.txt).
+template <bool TRACE, bool COUNT, bool STATS = false>
 __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_render_sched_kernel(const RenderArgs A)
 {
     __shared__ float bb[1504];
@@ -149,6 +152,11 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     } else {
                         float* film = reinterpret_cast<float*>(__ldcg(reinterpret_cast<const unsigned long long*>(&A.ring[cold[C_RANGE][lane_col] % RING_SLOTS].film))); // the film of the call this job belongs to
                         film_add(film + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)) * 4, S.imaging_ratio * L.x, S.imaging_ratio * L.y, S.imaging_ratio * L.z);
+                        if (STATS) {
+                            float* sq = reinterpret_cast<float*>(__ldcg(reinterpret_cast<const unsigned long long*>(&A.ring[cold[C_RANGE][lane_col] % RING_SLOTS].sum_y2)));
+                            const float yl = S.imaging_ratio * L.y;
+                            if (sq) atomicAdd(sq + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)), yl * yl);
+                        }
                     }
                     pixel_open = false;
                 }
@@ -184,7 +192,12 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         if (TRACE) jid = A.trace_jids[j];
                         else {
                             const uint64_t tcount = __ldcg(&R->tile_count);
-                            const uint64_t k = j / tcount, tile_k = __ldcg(&R->tile_begin) + (j - k * tcount);
+                            const uint64_t k = j / tcount;
+                            uint64_t tile_k = __ldcg(&R->tile_begin) + (j - k * tcount);
+                            if (STATS) {
+                                const uint32_t* list = reinterpret_cast<const uint32_t*>(__ldcg(reinterpret_cast<const unsigned long long*>(&R->tile_list)));
+                                if (list) tile_k = __ldg(list + (j - k * tcount));
+                            }
                             jid = (uint64_t(__ldcg(&R->first_wave) - 1u) + k * __ldcg(&R->wave_stride)) * S.ntiles + tile_k;
                         }
                         const uint64_t tile = jid % S.ntiles;

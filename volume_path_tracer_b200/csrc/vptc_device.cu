@@ -134,6 +134,8 @@ struct RangeSpec {
     float* film = nullptr;
     unsigned long long n_jobs = 0, tile_begin = 0, tile_count = 0;
     uint32_t first_wave = 1, wave_stride = 1;
+    // statistics launches (adaptive rendering): explicit tile list, second-moment plane; run the STATS instantiation of the default kernel
+    const uint32_t* tile_list = nullptr; float* sum_y2 = nullptr; bool stats = false;
 };
 
 // Publish a range into the device ring (descriptor first, then the tail, both on the control stream, which runs beside any render kernel
@@ -145,6 +147,7 @@ int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
     d.counter = 0; d.done = 0; d.n_jobs = r.n_jobs; d.film = r.film;
     d.tile_begin = r.tile_begin; d.tile_count = r.tile_count;
     d.first_wave = r.first_wave; d.wave_stride = r.wave_stride; d.rid = id; d.pad_ = 0;
+    d.tile_list = r.tile_list; d.sum_y2 = r.sum_y2;
     ctx->h_tail[slot] = id + 1;
     ctx->h_done[slot] = 0;
     CU(cudaMemcpyAsync(ctx->d_ring + slot, &d, sizeof(RangeDesc), cudaMemcpyHostToDevice, ctx->ctl));
@@ -172,8 +175,9 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
         return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile range outside the frame's tiles");
     // variant 3 packs pixel coordinates into 16-bit halves of its slot words: larger frames / tiles take variant 2
     int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
-    if (variant != 2 && !trace && r.tile_count != A.scene.ntiles) variant = 2; // tile stripes exist in the default kernel only
-    int per_sm = render_blocks_per_sm(variant, trace, ctx->count);
+    if (variant != 2 && !trace && (r.tile_count != A.scene.ntiles || r.stats)) variant = 2; // tile stripes / lists exist in the default kernel only
+    const bool stats = r.stats && !trace && !ctx->count;
+    int per_sm = stats ? render_stats_blocks_per_sm() : render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
@@ -193,7 +197,7 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
     A.exited = ctx->d_exited; A.exit_limit = unsigned(blocks) * unsigned(per_block) / 2u;
     CU(cudaMemsetAsync(ctx->d_exited, 0, sizeof(unsigned int), ctx->stream)); // same stream: runs between the previous launch and this one
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
+    CU(stats ? launch_render_stats(A, blocks, ctx->stream) : launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     return VPTC_OK;
 }
@@ -519,6 +523,72 @@ int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uin
     ctx->last_ms = 0.0f;
     if (int rc = vptc_render_async(ctx, scene, first_wave, n_waves, film_xyzw)) return rc;
     return wait_all(ctx);
+}
+
+int vptc_render_adaptive(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, const vptc_adaptive_params* p, float* film_xyzw, float* sum_y2, uint32_t* tile_waves)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_adaptive: ctx is null");
+    if (!ctx->has_volume) return fail(ctx, VPTC_ERR_NO_VOLUME, "no volume set: call vptc_set_volume first");
+    if (int rc = check_scene(ctx, scene)) return rc;
+    if (!p || !film_xyzw || first_wave < 1 || p->batch_waves < 1 || !(p->rel_error >= 0.0f)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_adaptive: null argument, first_wave < 1, batch_waves < 1 or rel_error < 0");
+    CU(cudaSetDevice(ctx->device));
+    if (int rc = wait_all(ctx)) return rc;
+    SceneDev sd; vpt_host::prepare_scene(*scene, ctx->has_temperature, sd);
+    if (sd.ntiles > 0xffffffffull) return fail(ctx, VPTC_ERR_UNSUPPORTED, "vptc_render_adaptive: more than 2^32 - 1 tiles");
+    const size_t npx = size_t(sd.W) * size_t(sd.H), nt = size_t(sd.ntiles);
+    float *d_film = nullptr, *d_sq = nullptr, *d_err = nullptr; uint32_t* d_list = nullptr;
+    auto cleanup = [&]() { cudaFree(d_film); cudaFree(d_sq); cudaFree(d_err); cudaFree(d_list); };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_film, npx * 16)) != cudaSuccess || (e = cudaMalloc(&d_sq, npx * 4)) != cudaSuccess || (e = cudaMalloc(&d_err, nt * 4)) != cudaSuccess ||
+        (e = cudaMalloc(&d_list, nt * 4)) != cudaSuccess || (e = cudaMemsetAsync(d_film, 0, npx * 16, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(d_sq, 0, npx * 4, ctx->stream)) != cudaSuccess) {
+        cleanup(); return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_render_adaptive: ") + cudaGetErrorString(e));
+    }
+    std::vector<uint32_t> active(nt), waves(nt, 0u);
+    for (size_t t = 0; t < nt; ++t) active[t] = uint32_t(t);
+    std::vector<float> err(nt);
+    uint32_t wave = first_wave, remaining = p->max_waves;
+    float total_ms = 0.0f;
+    int rc = VPTC_OK;
+    bool list_dirty = false; // the first batch covers every tile: a contiguous range, no list
+    while (rc == VPTC_OK && remaining > 0 && !active.empty()) {
+        const uint32_t b = std::min(p->batch_waves, remaining);
+        if (list_dirty) {
+            if ((e = cudaMemcpyAsync(d_list, active.data(), active.size() * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) { rc = fail(ctx, VPTC_ERR_CUDA, cudaGetErrorString(e)); break; }
+            if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) { rc = fail(ctx, VPTC_ERR_CUDA, cudaGetErrorString(e)); break; }
+        }
+        RenderArgs A{};
+        RangeSpec r;
+        r.film = d_film; r.sum_y2 = d_sq; r.stats = true; r.first_wave = wave; r.wave_stride = 1;
+        r.tile_begin = 0; r.tile_count = active.size(); r.tile_list = active.size() == nt ? nullptr : d_list;
+        r.n_jobs = (unsigned long long)active.size() * b;
+        if ((rc = run_render(ctx, scene, A, r, /*trace=*/false)) != VPTC_OK) break;
+        total_ms += ctx->last_ms;
+        for (uint32_t t : active) waves[t] += b;
+        wave += b; remaining -= b;
+        if (p->rel_error > 0.0f && remaining > 0 && waves[active[0]] >= std::max(2u, p->min_waves)) { // stop_at_next_wave, per tile (tile_provider.cpp:107-111)
+            if ((e = launch_tile_error(d_film, d_sq, sd.W, sd.H, sd.tw, sd.th, sd.ntx, sd.ntiles, d_err, ctx->stream)) != cudaSuccess ||
+                (e = cudaMemcpyAsync(err.data(), d_err, nt * 4, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess || (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) {
+                rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_render_adaptive: ") + cudaGetErrorString(e)); break;
+            }
+            std::vector<uint32_t> keep;
+            for (uint32_t t : active) if (!(err[t] <= p->rel_error)) keep.push_back(t);
+            if (keep.size() != active.size()) { active.swap(keep); list_dirty = true; }
+        }
+    }
+    if (rc == VPTC_OK) {
+        std::vector<float> h(npx * 4);
+        if ((e = cudaMemcpy(h.data(), d_film, npx * 16, cudaMemcpyDeviceToHost)) != cudaSuccess) rc = fail(ctx, VPTC_ERR_CUDA, cudaGetErrorString(e));
+        else host_add(film_xyzw, h.data(), npx * 4);
+        if (rc == VPTC_OK && sum_y2) {
+            if ((e = cudaMemcpy(h.data(), d_sq, npx * 4, cudaMemcpyDeviceToHost)) != cudaSuccess) rc = fail(ctx, VPTC_ERR_CUDA, cudaGetErrorString(e));
+            else host_add(sum_y2, h.data(), npx);
+        }
+        if (rc == VPTC_OK && tile_waves) std::memcpy(tile_waves, waves.data(), nt * 4);
+    }
+    ctx->last_ms = total_ms;
+    cleanup();
+    return rc;
 }
 
 float vptc_last_render_ms(const vptc_ctx* ctx) { return ctx ? ctx->last_ms : 0.0f; }
