@@ -300,9 +300,9 @@ def strong_scaling(args, r, rank, world, local, barrier):
                 if count:
                     r.run_device(scene, film.data_ptr(), first, count, stride)
             else:
-                tb, tc, _, _ = shard_tile_rows(scene, me, n_ranks)
+                tb, tc, stride, _ = shard_tile_rows(scene, me, n_ranks)
                 if tc:
-                    r.run_device_range(scene, film.data_ptr(), 1, total, 1, tile_begin=tb, tile_count=tc)
+                    r.run_device_range(scene, film.data_ptr(), 1, total, 1, tile_begin=tb, tile_count=tc, tile_row_stride=stride)
             if n_ranks > 1:
                 ev[0].record()
                 if mode == "waves":
@@ -336,7 +336,7 @@ def strong_scaling(args, r, rank, world, local, barrier):
         if rank == 0:
             tn, coll_ms = float(tt[0]), float(tt[1])
             px = W * H * total
-            out["jobs"].append({"config": cfg, "frame": [W, H], "total_waves": total, "sharding": "waves + NCCL reduce" if mode == "waves" else "tile-row stripes + NCCL gather",
+            out["jobs"].append({"config": cfg, "frame": [W, H], "total_waves": total, "sharding": "waves + NCCL reduce" if mode == "waves" else "interleaved rows of tiles + NCCL gather",
                                 "pixel_samples": px, "t_n1_s": t1, "t_s": tn, "value_n1": px / t1, "value": px / tn, "speedup_vs_n1": t1 / tn, "efficiency_vs_n1": t1 / (tn * world),
                                 "collective_ms": coll_ms, "collective_share": coll_ms * 1e-3 / tn, "waves_per_gpu": total / world if mode == "waves" else total,
                                 "sample_counts_equal": counts_ok and bool((pinned[..., 3] == total).all()),

@@ -118,11 +118,14 @@ VPTC_API int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t
 
 /* A slice of the (tile, wave) job space: waves first_wave + k*wave_stride, k < n_waves, of the tiles [tile_begin, tile_begin + tile_count)
  * (row-major tile indices as TileProvider::compute_tile_rect numbers them, src/tile_provider.cpp:95-105; tile_count 0 = every tile).
+ * tile_row_stride > 1 makes the slice an INTERLEAVED stripe: tile_begin and tile_count must be multiples of the tiles per row, and the
+ * slice's rows of tiles are tile_begin/ntx, + tile_row_stride, + 2*tile_row_stride, ... (G devices taking every G-th row share the
+ * expensive part of a frame evenly; 0 and 1 both mean a contiguous slice).
  * Job ids stay (wave-1)*ntiles + tile whatever the slice, so any partition of the job space — by waves, by tile stripes, across calls or
  * across GPUs — renders exactly the samples one vptc_render call over the whole space would. */
 typedef struct vptc_job_range {
     uint32_t first_wave, n_waves, wave_stride;
-    uint32_t reserved;
+    uint32_t tile_row_stride;
     uint64_t tile_begin, tile_count;
 } vptc_job_range;
 
@@ -162,8 +165,9 @@ VPTC_API int vptc_render_adaptive(vptc_ctx* ctx, const vptc_scene* scene, uint32
  * device over peer memory (NVLink / NVSwitch):
  *   VPTC_SHARD_WAVES  device g of G renders waves first + g, first + g + G, ... of the whole frame; the partial films are SUMMED by a kernel on
  *                     the first device that reads the other films in place through peer mappings (progressive rendering, high spp);
- *   VPTC_SHARD_TILES  device g renders all waves of one stripe of tile rows (src/tile_provider.cpp:95-105); the stripes are GATHERED with
- *                     peer copies: disjoint pixels, 1/G of the film each (low spp, large frames).
+ *   VPTC_SHARD_TILES  device g renders all waves of every G-th ROW of tiles, g, g + G, ... (src/tile_provider.cpp:95-105; interleaved so that the
+ *                     devices share the expensive part of the frame); the rows are GATHERED with peer copies: disjoint pixels, 1/G of the film
+ *                     each, no arithmetic (low spp, large frames).
  * Job ids are those of the single-device render either way, so sample counts are equal and radiance differs only by fp32 add order.
  * vptc_group_render_async enqueues on every device and returns; vptc_group_wait finishes everything enqueued since the last wait, combines
  * and ADDS the result into the caller's host film. vptc_group_render = both. Frame size and sharding must not change between waits. */
@@ -262,6 +266,15 @@ VPTC_API void vptc_free(void* p);
  * of the box centre (centre of the base for "fire"). temperature may be NULL. */
 VPTC_API int vptc_synth_volume(const char* kind, const int32_t dims[3], double voxel_size, uint32_t seed, const double* anchor_xyz,
                                void** density, size_t* density_bytes, void** temperature, size_t* temperature_bytes);
+
+/* Debug front-end = Volume::log_dda_trace (src/volume.cpp:194-225; the third of the reference's CSV traces, beside vptc_trace_pixel_csv and
+ * vptc_trace_path_log): the per-VOXEL ground truth along a ray — X,Y,Z,T,Value,Dim_getdim,Dim_nodeinfo,Active,Maximum, one row per voxel a
+ * dim-1 DDA visits from 16 index units before the ray enters the grid's index bounding box to 16 after it leaves — in the reference's number
+ * formatting, so scripts/plot_dda_trace.py reads it. Host code on the caller's NanoVDB buffer (value masks and node statistics are not in the
+ * baked device layout). The pixel form traces the un-jittered camera ray through the centre of pixel (px, py). A ray that misses the grid
+ * writes no file, like the reference; *n_rows (may be NULL) receives the number of voxel rows. */
+VPTC_API int vptc_dda_trace_csv(const void* density_grid, size_t density_bytes, const vptc_scene* scene, int64_t px, int64_t py, const char* csv_path, size_t* n_rows);
+VPTC_API int vptc_dda_trace_ray_csv(const void* density_grid, size_t density_bytes, const float origin_xyz[3], const float direction_xyz[3], const char* csv_path, size_t* n_rows);
 
 /* 8-bit RGB PNG (replaces Image<uchar,3>::save, src/image_io.cpp:18-58). */
 VPTC_API int vptc_write_png(const char* path, const uint8_t* rgb8, int64_t width, int64_t height);

@@ -246,6 +246,7 @@ class Reference:
         L.vptr_trace_segments.argtypes = [vp, vp, vp, sz, C.c_uint32, vp, vp]
         L.vptr_sample_collisions.argtypes = [vp, C.c_uint32, vp, vp, vp, sz, C.c_float, C.c_uint32, vp, vp]
         L.vptr_tile_rects.argtypes = [vp, vp, sz, C.POINTER(sz)]
+        L.vptr_log_dda_trace.argtypes = [vp, vp, vp]
         L.vptr_rng.argtypes = [C.c_uint32, C.c_uint64, sz, C.POINTER(C.c_uint64), vp, vp]
         L.vptr_rng.restype = None
         L.vptr_camera_rays.argtypes = [vp, sz, vp, vp, vp, vp, vp, vp]
@@ -359,6 +360,21 @@ class ReferenceVolume:
         if rc != 0:
             raise RuntimeError(f"vptr_trace_segments failed ({rc})")
         return segs, n
+
+    def log_dda_trace(self, origin, direction, workdir) -> str:
+        """Volume::log_dda_trace: the reference writes ./dda_trace.csv; run it with `workdir` as the current directory. -> the file's text ('' if none)."""
+        o, d = np.ascontiguousarray(origin, np.float32), np.ascontiguousarray(direction, np.float32)
+        cwd = os.getcwd()
+        os.chdir(workdir)
+        try:
+            p = Path("dda_trace.csv")
+            if p.exists():
+                p.unlink()
+            if self.L.vptr_log_dda_trace(self.ctx, _ptr(o), _ptr(d)) != 0:
+                raise RuntimeError("vptr_log_dda_trace failed")
+            return p.read_text() if p.exists() else ""
+        finally:
+            os.chdir(cwd)
 
     def sample_collisions(self, seed: int, jids, origins, dirs, sigma_t: float, max_hits: int = 64):
         """MajorantTransmittanceSampler::next along world rays -> (hits[n, max_hits, 5] = point xyz, sigma_maj, density; n_hits)."""

@@ -196,6 +196,17 @@ int vptr_sample_collisions(void* ctx, uint32_t seed, const uint64_t* jids, const
     return 0;
 }
 
+// Volume::log_dda_trace (volume.cpp:194-225): writes "dda_trace.csv" into the CURRENT DIRECTORY (the reference hard-codes the name).
+int vptr_log_dda_trace(void* ctx, const float* origin, const float* dir)
+{
+    auto* c = static_cast<Ctx*>(ctx);
+    if (!c) return -1;
+    vpt::Volume vol(*c->grids, vpt::VolumeParameters{});
+    auto acc = c->grids->density().getAccessor();
+    vol.log_dda_trace(vpt::Ray(v3(origin), v3(dir)), acc);
+    return 0;
+}
+
 // TileProvider::next / token::compute_rect for wave 1 (tile_provider.cpp:27-67,95-105): {x0, y0, w, h, jid} per tile, in hand-out order.
 int vptr_tile_rects(const vptc_scene* s, int64_t* out5, size_t cap, size_t* n_out)
 {

@@ -29,12 +29,12 @@ def test_shard_waves_partition():
         scene, _ = scenes.small_variant("fire", size, 1, 0.25)
         scene.tile_size[0], scene.tile_size[1] = tile
         spans = [shard_tile_rows(scene, r, world) for r in range(world)]
-        assert spans[0][0] == 0 and spans[-1][0] + spans[-1][1] == scene.ntiles          # tiles: contiguous, complete
-        assert all(a[0] + a[1] == b[0] for a, b in zip(spans, spans[1:]))
-        assert spans[0][2] == 0 and spans[-1][3] == size[1]                                # film rows: contiguous bands
-        assert all(a[3] == b[2] for a, b in zip(spans, spans[1:]))
-        ntx = -(-size[0] // tile[0])
-        assert all(tb % ntx == 0 and tc % ntx == 0 and y0 == min(size[1], tb // ntx * tile[1]) for tb, tc, y0, y1 in spans)
+        ntx, nty = -(-size[0] // tile[0]), -(-size[1] // tile[1])
+        assert sum(tc for _, tc, _, _ in spans) == scene.ntiles                             # every tile exactly once
+        assert all(tb == r * ntx and tc % ntx == 0 and st == world for r, (tb, tc, st, _) in enumerate(spans))
+        rows = sorted(y for _, _, _, sl in spans for s in sl for y in range(s.start, s.stop))
+        assert rows == list(range(size[1]))                                                  # every film row exactly once
+        assert all(len(sl) == tc // ntx for _, tc, _, sl in spans)
     with pytest.raises(ValueError):
         shard_waves(0, 4, 0, 2)
     with pytest.raises(ValueError):
@@ -74,11 +74,12 @@ def _worker(rank, world, port, out_path):
         render_sharded(rr, scene, acc, 1, 3, rank, world)
         render_sharded(rr, scene, acc, 4, 2, rank, world)
         # tile-row stripes of wave 2, gathered
-        tb, tc, y0, y1 = shard_tile_rows(scene, rank, world)
+        tb, tc, stride, bands = shard_tile_rows(scene, rank, world)
         stripes = torch.zeros_like(acc)
         wave2 = np.zeros_like(film)
         vol.render(scene, wave2, first_wave=2, n_waves=1, threads=2)
-        stripes[y0:y1] = torch.from_numpy(wave2)[y0:y1]   # this rank's band only
+        for sl in bands:
+            stripes[sl] = torch.from_numpy(wave2)[sl]   # this rank's rows of tiles only
         gather_film_stripes(stripes, scene, rank, world)
         if rank == 0:
             full = np.zeros_like(film)

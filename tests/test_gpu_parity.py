@@ -564,6 +564,17 @@ def test_device_async_series_and_tile_stripes(renderer, loaded):
     renderer.run_device_range(scene, stripe.data_ptr(), 1, 2, 1, tile_begin=ntx, tile_count=2 * ntx)  # tile rows 1 and 2
     th = int(scene.tile_size[1])
     assert bool((stripe[th:3 * th, :, 3] == 2).all()) and float(stripe[:th].abs().sum()) == 0 and float(stripe[3 * th:].abs().sum()) == 0
+    # interleaved stripes (tile_row_stride): three "devices" taking every third row of tiles cover the frame exactly once
+    nty = -(-H // th)
+    inter = torch.zeros_like(whole)
+    for d in range(3):
+        rows = len(range(d, nty, 3))
+        renderer.run_device_range(scene, inter.data_ptr(), 1, 1, 1, tile_begin=d * ntx, tile_count=rows * ntx, tile_row_stride=3, wait=False)
+    renderer.wait()
+    torch.cuda.synchronize()
+    assert torch.equal(inter, whole)
+    with pytest.raises(Exception):
+        renderer.run_device_range(scene, inter.data_ptr(), 1, 1, 1, tile_begin=2 * ntx, tile_count=nty * ntx, tile_row_stride=3)
     # waves as a series of async calls, interleaved strides
     series = torch.zeros_like(whole)
     for first in (1, 2, 3):
@@ -587,7 +598,9 @@ def test_adaptive_render_contract(renderer, loaded):
     f1, sq1, tw1 = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=1, batch_waves=1, rel_error=0.0)
     plain1 = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=1)
     assert np.array_equal(f1, plain1) and (tw1 == 1).all()
-    assert np.array_equal(sq1, plain1[..., 1] * plain1[..., 1])
+    y2 = plain1[..., 1] * plain1[..., 1]
+    normal = y2 >= np.float32(1.2e-38)  # atomic float adds flush subnormal operands to zero
+    assert np.array_equal(sq1[normal], y2[normal]) and (sq1[~normal] <= y2[~normal]).all()
     # never stopping, many waves
     f, sq, tw = renderer.run_adaptive(scene, renderer.new_film(scene), max_waves=24, batch_waves=8, rel_error=0.0)
     plain = renderer.run(scene, renderer.new_film(scene), first_wave=1, n_waves=24)

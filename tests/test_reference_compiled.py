@@ -186,3 +186,28 @@ def test_golden_vectors_hold_for_the_compiled_reference(reference, small_case, s
         film = np.zeros((scene.height, scene.width, 4), np.float32)
         rv.render(scene, film, threads=4)
         assert np.array_equal(film, gold[f"{name}_film"])
+
+
+@pytest.mark.parametrize("name", ["fire", "wdas_cloud"])
+def test_dda_trace_csv_equals_the_references(reference, api, small_case, tmp_path, name):
+    """vptc_dda_trace_csv (host code on the NanoVDB buffer) writes the file Volume::log_dda_trace writes (volume.cpp:194-225), character for
+    character: voxel coordinates, DDA times, values, getDim, NodeInfo dim, active state and node maxima along camera rays and a miss."""
+    scene, spec, grids = small_case(name)
+    rv = reference.volume(grids)
+    rs = np.random.default_rng(4)
+    n_rows = 0
+    for k in range(6):
+        px, py = int(rs.integers(0, scene.width)), int(rs.integers(0, scene.height))
+        o, d = reference.camera_rays(scene, [px], [py], [0.0], [0.0])
+        want = rv.log_dda_trace(o[0], d[0], tmp_path)
+        mine = tmp_path / f"mine_{k}.csv"
+        rows = api.dda_trace_csv(grids, mine, scene, px, py)
+        got = mine.read_text() if mine.exists() else ""
+        assert got == want
+        assert rows == max(0, len(want.splitlines()) - 1)
+        n_rows += rows
+    assert n_rows > 100
+    # an explicit ray that misses the volume: no file from either
+    o, d = np.array([1e4, 1e4, 1e4], np.float32), np.array([0, 1, 0], np.float32)
+    assert rv.log_dda_trace(o, d, tmp_path) == ""
+    assert api.dda_trace_csv(grids, tmp_path / "miss.csv", origin=o, direction=d) == 0 and not (tmp_path / "miss.csv").exists()

@@ -83,7 +83,7 @@ class Counters(C.Structure):
 
 class JobRange(C.Structure):
     """vptc_job_range: waves first_wave + k*wave_stride (k < n_waves) of the tiles [tile_begin, tile_begin + tile_count); tile_count 0 = all."""
-    _fields_ = [("first_wave", C.c_uint32), ("n_waves", C.c_uint32), ("wave_stride", C.c_uint32), ("reserved", C.c_uint32),
+    _fields_ = [("first_wave", C.c_uint32), ("n_waves", C.c_uint32), ("wave_stride", C.c_uint32), ("tile_row_stride", C.c_uint32),
                 ("tile_begin", C.c_uint64), ("tile_count", C.c_uint64)]
 
 
@@ -102,13 +102,13 @@ EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_render_adaptive", "vptc_last_render_ms", "vptc_device_volume_bytes",
     "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
-    "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_host_last_error",
+    "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_host_last_error", "vptc_dda_trace_csv", "vptc_dda_trace_ray_csv",
     "vptc_group_create", "vptc_group_destroy", "vptc_group_last_error", "vptc_group_size", "vptc_group_peer_mapped", "vptc_group_set_volume", "vptc_group_render",
     "vptc_group_render_async", "vptc_group_wait", "vptc_group_last_render_ms", "vptc_group_context",
 ]
 
 HOST_EXPORTS = ["vptc_host_last_error", "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
-                "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version"]
+                "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_dda_trace_csv", "vptc_dda_trace_ray_csv"]
 HOST_LIB_PATH = _PKG / "libvpthost.so"
 
 _lib = None
@@ -129,6 +129,8 @@ def _declare_host(L):
     L.vptc_write_png.argtypes = [C.c_char_p, vp, C.c_int64, C.c_int64]
     L.vptc_film_save.argtypes = [C.c_char_p, C.POINTER(Scene), vp, u32]
     L.vptc_film_load.argtypes = [C.c_char_p, C.POINTER(Scene), vp, C.POINTER(u32)]
+    L.vptc_dda_trace_csv.argtypes = [vp, sz, C.POINTER(Scene), C.c_int64, C.c_int64, C.c_char_p, C.POINTER(sz)]
+    L.vptc_dda_trace_ray_csv.argtypes = [vp, sz, vp, vp, C.c_char_p, C.POINTER(sz)]
 
 
 def host_lib() -> C.CDLL:
@@ -290,6 +292,18 @@ def scene_from_json(text: str):
     return s, buf.value.decode()
 
 
+def dda_trace_csv(grids: "VolumeGrids", path, scene: "Scene" = None, px: int = 0, py: int = 0, origin=None, direction=None) -> int:
+    """dda_trace.csv (Volume::log_dda_trace, volume.cpp:194-225) of the camera ray through pixel (px, py), or of an explicit world ray.
+    -> number of voxel rows written (0 and no file when the ray misses the grid)."""
+    n = C.c_size_t(0)
+    if origin is not None:
+        o, d = np.ascontiguousarray(origin, np.float32), np.ascontiguousarray(direction, np.float32)
+        _check_host(host_lib().vptc_dda_trace_ray_csv(grids.density.ptr, grids.density.nbytes, _ptr(o), _ptr(d), str(path).encode(), C.byref(n)))
+    else:
+        _check_host(host_lib().vptc_dda_trace_csv(grids.density.ptr, grids.density.nbytes, C.byref(scene), int(px), int(py), str(path).encode(), C.byref(n)))
+    return int(n.value)
+
+
 def write_png(path, rgb: np.ndarray):
     rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
     _check_host(host_lib().vptc_write_png(str(path).encode(), _ptr(rgb), rgb.shape[1], rgb.shape[0]))
@@ -366,9 +380,9 @@ class Renderer:
         _check(lib().vptc_render_device(self._ctx, C.byref(scene), first_wave, n_waves, wave_stride, C.c_void_p(d_film_ptr)), self._ctx)
 
     def run_device_range(self, scene: Scene, d_film_ptr: int, first_wave: int, n_waves: int, wave_stride: int = 1, tile_begin: int = 0, tile_count: int = 0,
-                         wait: bool = True):
+                         wait: bool = True, tile_row_stride: int = 1):
         """A slice of the job space (vptc_job_range) into a device film; wait=False enqueues (vptc_render_device_async) — finish with wait()."""
-        jr = JobRange(first_wave, n_waves, wave_stride, 0, tile_begin, tile_count)
+        jr = JobRange(first_wave, n_waves, wave_stride, tile_row_stride, tile_begin, tile_count)
         fn = lib().vptc_render_device_range if wait else lib().vptc_render_device_async
         _check(fn(self._ctx, C.byref(scene), C.byref(jr), C.c_void_p(d_film_ptr)), self._ctx)
 

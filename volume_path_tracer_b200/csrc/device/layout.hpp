@@ -72,7 +72,9 @@ struct SceneDev {
 // takes jobs from its own call's range and, when that is exhausted, carries on into the next published one instead of draining — so a
 // progressive render made of many small calls keeps every lane busy across call boundaries (DESIGN.md "launch drain"). A range may also
 // cover only a stripe of tiles [tile_begin, tile_begin + tile_count) (multi-GPU tile sharding, src/tile_provider.cpp:95-105).
-//   job j of the range:  k = j / tile_count,  tile = tile_begin + j % tile_count,  jid = (first_wave - 1 + k * wave_stride) * ntiles + tile
+//   job j of the range:  k = j / tile_count,  i = j % tile_count,  tile = tile_begin + (i / ntx) * tile_row_stride * ntx + i % ntx,
+//                        jid = (first_wave - 1 + k * wave_stride) * ntiles + tile
+//   (tile_row_stride 1: the contiguous stripe; G: every G-th ROW of tiles starting at row tile_begin / ntx — interleaved stripes balance the load)
 constexpr unsigned RING_SLOTS = 64;
 struct RangeDesc { // 80 bytes
     unsigned long long counter;  // next job index of the range = TileProvider::m_job_idx (tile_provider.cpp:28); device atomics only
@@ -81,7 +83,7 @@ struct RangeDesc { // 80 bytes
     float* film;                 // H*W*4 floats this range accumulates into
     unsigned long long tile_begin, tile_count;
     uint32_t first_wave, wave_stride;
-    uint32_t rid, pad_;          // absolute range number (slot = rid % RING_SLOTS)
+    uint32_t rid, tile_row_stride; // absolute range number (slot = rid % RING_SLOTS); rows of tiles to skip between the stripe's rows (>= 1)
     // statistics launches only (the STATS instantiation of the kernel; adaptive rendering):
     const uint32_t* tile_list;   // when set: the range covers tile_list[0 .. tile_count) instead of a contiguous stripe
     float* sum_y2;               // when set: H*W floats, += (imaging_ratio * L.y)^2 per pixel-sample (second moment of the luminance)

@@ -193,7 +193,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         else {
                             const uint64_t tcount = __ldcg(&R->tile_count);
                             const uint64_t k = j / tcount;
-                            uint64_t tile_k = __ldcg(&R->tile_begin) + (j - k * tcount);
+                            const uint64_t ti = j - k * tcount, trow = ti / uint64_t(S.ntx); // interleaved stripes: every tile_row_stride-th row of tiles
+                            uint64_t tile_k = __ldcg(&R->tile_begin) + trow * (uint64_t(__ldcg(&R->tile_row_stride)) * uint64_t(S.ntx)) + (ti - trow * uint64_t(S.ntx));
                             if (STATS) {
                                 const uint32_t* list = reinterpret_cast<const uint32_t*>(__ldcg(reinterpret_cast<const unsigned long long*>(&R->tile_list)));
                                 if (list) tile_k = __ldg(list + (j - k * tcount));

@@ -61,6 +61,13 @@ int main(int argc, char* argv[])
         temperature = nullptr; temperature_bytes = 0;
     }
 
+    if (const char* tp = std::getenv("VPT_TRACE_PIXEL")) { // dda_trace.csv needs the NanoVDB buffer itself (masks, node statistics): before it is freed
+        long long tx = -1, ty = -1;
+        size_t rows = 0;
+        if (std::sscanf(tp, "%lld,%lld", &tx, &ty) != 2) vptFATAL("VPT_TRACE_PIXEL must be \"x,y\"");
+        if (vptc_dda_trace_csv(density, density_bytes, &cfg, tx, ty, "dda_trace.csv", &rows) != VPTC_OK) vptFATAL(vptc_last_error(nullptr));
+        vptINFO("Wrote dda_trace.csv for pixel (" << tx << ", " << ty << "): " << rows << " voxels");
+    }
     // Devices. VPT_DEVICES=0,1,2,... renders on several GPUs behind one vptc_group (the reference drives all its workers from main(),
     // src/main.cpp:63-87): volume replicated, job space sharded by waves (VPT_SHARD=waves, default) or by stripes of tile rows
     // (VPT_SHARD=tiles), films combined on the first device. VPT_DEVICE=n (or nothing) renders on one GPU.

@@ -129,11 +129,21 @@ int check_scene(vptc_ctx* ctx, const vptc_scene* s)
     return VPTC_OK;
 }
 
+// A tile slice must stay inside the frame: contiguous [begin, begin + count), or — with a row stride — whole rows of tiles begin/ntx, +stride, ...
+bool range_inside(const SceneDev& sd, unsigned long long begin, unsigned long long count, uint32_t row_stride)
+{
+    if (row_stride <= 1) return begin <= sd.ntiles && count <= sd.ntiles - begin;
+    const unsigned long long ntx = (unsigned long long)sd.ntx, nty = (unsigned long long)sd.nty;
+    if (begin % ntx != 0 || count % ntx != 0) return false; // interleaved stripes are made of whole rows
+    const unsigned long long row0 = begin / ntx, rows = count / ntx;
+    return rows == 0 || (row0 < nty && row0 + (rows - 1) * row_stride < nty);
+}
+
 // What one render call covers. tile_count == 0 means every tile of the frame.
 struct RangeSpec {
     float* film = nullptr;
     unsigned long long n_jobs = 0, tile_begin = 0, tile_count = 0;
-    uint32_t first_wave = 1, wave_stride = 1;
+    uint32_t first_wave = 1, wave_stride = 1, tile_row_stride = 1;
     // statistics launches (adaptive rendering): explicit tile list, second-moment plane; run the STATS instantiation of the default kernel
     const uint32_t* tile_list = nullptr; float* sum_y2 = nullptr; bool stats = false;
 };
@@ -146,7 +156,7 @@ int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
     RangeDesc& d = ctx->h_ring[slot];
     d.counter = 0; d.done = 0; d.n_jobs = r.n_jobs; d.film = r.film;
     d.tile_begin = r.tile_begin; d.tile_count = r.tile_count;
-    d.first_wave = r.first_wave; d.wave_stride = r.wave_stride; d.rid = id; d.pad_ = 0;
+    d.first_wave = r.first_wave; d.wave_stride = r.wave_stride; d.rid = id; d.tile_row_stride = std::max(1u, r.tile_row_stride);
     d.tile_list = r.tile_list; d.sum_y2 = r.sum_y2;
     ctx->h_tail[slot] = id + 1;
     ctx->h_done[slot] = 0;
@@ -171,11 +181,10 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
     for (int i = 0; i < 4; ++i) A.sched_thresh[i] = std::max(1, ctx->sched_thresh[i]); // the kernel relies on >= 1
     for (int i = 0; i < 4; ++i) A.pool_params[i] = std::max(1, ctx->pool_params[i]);
     if (r.tile_count == 0) { r.tile_begin = 0; r.tile_count = A.scene.ntiles; }
-    if (!trace && (r.tile_begin > A.scene.ntiles || r.tile_count > A.scene.ntiles - r.tile_begin))
-        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile range outside the frame's tiles");
+    if (!trace && !range_inside(A.scene, r.tile_begin, r.tile_count, r.tile_row_stride)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "tile range outside the frame's tiles");
     // variant 3 packs pixel coordinates into 16-bit halves of its slot words: larger frames / tiles take variant 2
     int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
-    if (variant != 2 && !trace && (r.tile_count != A.scene.ntiles || r.stats)) variant = 2; // tile stripes / lists exist in the default kernel only
+    if (variant != 2 && !trace && (r.tile_count != A.scene.ntiles || r.tile_row_stride > 1 || r.stats)) variant = 2; // tile stripes / lists exist in the default kernel only
     const bool stats = r.stats && !trace && !ctx->count;
     int per_sm = stats ? render_stats_blocks_per_sm() : render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
@@ -298,7 +307,8 @@ int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* 
     RangeSpec r;
     r.film = d_film; r.first_wave = jr->first_wave; r.wave_stride = jr->wave_stride;
     r.tile_begin = jr->tile_begin; r.tile_count = jr->tile_count ? jr->tile_count : sd.ntiles;
-    if (r.tile_begin > sd.ntiles || r.tile_count > sd.ntiles - r.tile_begin) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "render: tile range outside the frame's tiles");
+    r.tile_row_stride = std::max(1u, jr->tile_row_stride);
+    if (!range_inside(sd, r.tile_begin, r.tile_count, r.tile_row_stride)) return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "render: tile range outside the frame's tiles (a row stride takes whole rows of tiles)");
     r.n_jobs = r.tile_count * (unsigned long long)jr->n_waves;
     if (launched) *launched = false;
     if (rid) *rid = ~0u; // stays ~0 for the kernels that do not read the ring (variants 0, 1, 3)
@@ -470,7 +480,7 @@ int vptc_render_device_range(vptc_ctx* ctx, const vptc_scene* scene, const vptc_
 int vptc_render_device(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves, uint32_t wave_stride, void* d_film)
 {
     if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_render_device: ctx is null");
-    const vptc_job_range jr{first_wave, n_waves, wave_stride, 0, 0, 0};
+    const vptc_job_range jr{first_wave, n_waves, wave_stride, 1, 0, 0};
     return vptc_render_device_range(ctx, scene, &jr, d_film);
 }
 
@@ -503,7 +513,7 @@ int vptc_render_async(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wav
     CU(cudaMemcpyAsync(ctx->film[b], ctx->pinned_zero, n * sizeof(float), cudaMemcpyHostToDevice, ctx->ctl)); // cleared before the range is published (same stream)
     CU(cudaEventRecord(ctx->ev_ctl, ctx->ctl));
     CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_ctl, 0)); // kernels that do not read the ring (variants 0, 1, 3) are ordered after the clear by this
-    const vptc_job_range jr{first_wave, n_waves, 1, 0, 0, 0};
+    const vptc_job_range jr{first_wave, n_waves, 1, 1, 0, 0};
     unsigned int rid = ~0u;
     bool launched = false;
     if (int rc = enqueue_async(ctx, scene, &jr, ctx->film[b], &rid, &launched)) return rc;

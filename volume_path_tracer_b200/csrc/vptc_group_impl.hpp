@@ -4,9 +4,10 @@
 //
 //   VPTC_SHARD_WAVES  device g of G renders waves first + g, first + g + G, ... of the whole frame; the G partial films are SUMMED by
 //                     vpt_film_reduce_kernel on the first device, which reads the other devices' films directly through peer memory.
-//   VPTC_SHARD_TILES  device g renders every wave of one stripe of tile ROWS (src/tile_provider.cpp:95-105 numbers tiles row-major, so a
-//                     stripe of tile rows is one contiguous band of film rows); the bands are GATHERED with peer copies — disjoint pixels,
-//                     1/G of the bytes each, no arithmetic.
+//   VPTC_SHARD_TILES  device g renders every wave of the ROWS of tiles g, g + G, g + 2G, ... (src/tile_provider.cpp:95-105 numbers tiles
+//                     row-major, so a row of tiles is one contiguous band of tile_h film rows; interleaving the rows shares the expensive
+//                     part of the frame evenly — contiguous halves of the 4K cloud differed by 70 % in cost); the bands are GATHERED with
+//                     peer copies — disjoint pixels, 1/G of the bytes each, no arithmetic.
 // Job ids are unchanged by either partition (jid = (wave-1)*ntiles + tile), so the union of the devices' RNG streams is exactly the
 // single-GPU render: sample counts are equal, radiance sums differ only by fp32 add order.
 //
@@ -22,8 +23,7 @@ struct vptc_group {
     std::vector<char> peer;         // device 0 can read device g's memory directly
     bool dirty = false;             // something was rendered since the last wait
     int last_sharding = VPTC_SHARD_WAVES;
-    int64_t W = 0, H = 0, th = 1;
-    std::vector<int64_t> band_y0;   // VPTC_SHARD_TILES: first film row of each device's band (size G + 1)
+    int64_t W = 0, H = 0, th = 1, nty = 0;
     std::string error;
     float last_ms = 0.0f;
 };
@@ -155,18 +155,17 @@ int vptc_group_render_async(vptc_group* g, const vptc_scene* scene, uint32_t fir
     if (int rc = group_ensure_films(g, n)) return rc;
     const uint32_t G = uint32_t(g->ctx.size());
     g->W = scene->output_size[0]; g->H = scene->output_size[1]; g->th = th; g->last_sharding = sharding;
-    g->band_y0.assign(G + 1, 0);
-    for (uint32_t d = 0; d <= G; ++d) g->band_y0[d] = std::min<int64_t>(g->H, (nty * int64_t(d) / int64_t(G)) * th); // whole tile rows per device
+    g->nty = nty;
     for (uint32_t d = 0; d < G; ++d) {
         vptc_job_range jr{};
         if (sharding == VPTC_SHARD_WAVES) { // waves first + d, first + d + G, ...
             if (n_waves <= d) continue;
             jr.first_wave = first_wave + d; jr.n_waves = (n_waves - d + G - 1) / G; jr.wave_stride = G;
         } else {
-            const int64_t r0 = nty * int64_t(d) / int64_t(G), r1 = nty * int64_t(d + 1) / int64_t(G);
-            if (r1 <= r0) continue;
+            if (int64_t(d) >= nty) continue;
+            const int64_t rows = (nty - int64_t(d) + int64_t(G) - 1) / int64_t(G); // rows of tiles d, d + G, ...
             jr.first_wave = first_wave; jr.n_waves = n_waves; jr.wave_stride = 1;
-            jr.tile_begin = uint64_t(r0 * ntx); jr.tile_count = uint64_t((r1 - r0) * ntx);
+            jr.tile_begin = uint64_t(int64_t(d) * ntx); jr.tile_count = uint64_t(rows * ntx); jr.tile_row_stride = G;
         }
         if (int rc = enqueue_async(g->ctx[d], scene, &jr, g->film[d], nullptr)) return gfail(g, rc, "device " + std::to_string(g->ctx[d]->device) + ": " + g->ctx[d]->error);
     }
@@ -204,10 +203,13 @@ int vptc_group_wait(vptc_group* g, float* film_xyzw)
             GCU(launch_film_reduce(g->film[0], &src, 1, n / 4, c0->stream));
         }
     } else {
-        // GATHER: every device's band of film rows is copied into device 0's film (peer copy over NVLink); nothing is added
-        for (size_t d = 1; d < G; ++d) {
-            const size_t a = size_t(g->band_y0[d]) * size_t(g->W) * 4, b = size_t(g->band_y0[d + 1]) * size_t(g->W) * 4;
-            if (b > a) GCU(cudaMemcpyPeerAsync(g->film[0] + a, c0->device, g->film[d] + a, g->ctx[d]->device, (b - a) * sizeof(float), c0->stream));
+        // GATHER: every band (one row of tiles = tile_h film rows) is copied from the device that rendered it into device 0's film
+        // (peer copy over NVLink); nothing is added
+        for (int64_t row = 0; row < g->nty; ++row) {
+            const size_t d = size_t(row % int64_t(G));
+            if (d == 0) continue;
+            const size_t a = size_t(row * g->th) * size_t(g->W) * 4, b = size_t(std::min<int64_t>(g->H, (row + 1) * g->th)) * size_t(g->W) * 4;
+            GCU(cudaMemcpyPeerAsync(g->film[0] + a, c0->device, g->film[d] + a, g->ctx[d]->device, (b - a) * sizeof(float), c0->stream));
         }
     }
     GCU(cudaMemcpyAsync(g->pinned, g->film[0], n * sizeof(float), cudaMemcpyDeviceToHost, c0->stream));

@@ -1,5 +1,6 @@
 // vptc_host.cpp — the host-only entry points of include/vptc.h (no CUDA calls here):
 // .nvdb I/O, synthetic volumes, scene JSON, PNG. The device side lives in vptc_device.cu.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -7,10 +8,12 @@
 #include <string>
 #include <vector>
 
+#include "host/dda_trace.hpp"
 #include "host/json_scene.hpp"
 #include "host/nvdb_build.hpp"
 #include "host/nvdb_io.hpp"
 #include "host/png_write.hpp"
+#include "host/scene_prep.hpp"
 #include "host/synth.hpp"
 #include "vptc.h"
 #include "vptc_internal.hpp"
@@ -149,6 +152,42 @@ int vptc_film_save(const char* path, const vptc_scene* scene, const float* film_
     const bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(film_xyzw, sizeof(float), n, f) == n;
     const bool closed = std::fclose(f) == 0;
     if (!ok || !closed || std::rename(tmp.c_str(), path) != 0) { std::remove(tmp.c_str()); set_global_error(std::string("vptc_film_save: write failed for ") + path); return VPTC_ERR_IO; }
+    return VPTC_OK;
+}
+
+// Volume::log_dda_trace (src/volume.cpp:194-225) for the un-jittered camera ray through the centre of pixel (px, py): host code on the
+// caller's NanoVDB buffer (value masks and node statistics are not part of the baked device layout).
+int vptc_dda_trace_csv(const void* density_grid, size_t density_bytes, const vptc_scene* scene, int64_t px, int64_t py, const char* csv_path, size_t* n_rows)
+{
+    if (n_rows) *n_rows = 0;
+    if (!density_grid || !scene || !csv_path) { set_global_error("vptc_dda_trace_csv: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    if (scene->output_size[0] <= 0 || scene->output_size[1] <= 0 || scene->tile_size[0] <= 0 || scene->tile_size[1] <= 0 || px < 0 || py < 0 || px >= scene->output_size[0] ||
+        py >= scene->output_size[1]) { set_global_error("vptc_dda_trace_csv: pixel outside the image"); return VPTC_ERR_INVALID_ARGUMENT; }
+    vptd::SceneDev S;
+    vpt_host::prepare_scene(*scene, false, S);
+    // Camera::generate_ray (camera.hpp:14-23) with jitter 0: the kernels' arithmetic, on the host (-ffp-contract=off)
+    auto sum3 = [](float a, float b, float c) { return a + (b + c); };
+    const float rx = float(px) + 0.5f, ry = float(py) + 0.5f;
+    float d[3];
+    const float o[3] = {S.cam_pos[0], S.cam_pos[1], S.cam_pos[2]};
+    for (int r = 0; r < 3; ++r) d[r] = sum3(S.cam_m[r * 3] * rx, S.cam_m[r * 3 + 1] * ry, S.cam_m[r * 3 + 2] * 0.0f) + S.cam_t[r];
+    const float nrm = std::sqrt(sum3(d[0] * d[0], d[1] * d[1], d[2] * d[2]));
+    for (int r = 0; r < 3; ++r) d[r] /= nrm;
+    try {
+        const std::string err = vpt_host::write_dda_trace(density_grid, density_bytes, o, d, csv_path, n_rows);
+        if (!err.empty()) { set_global_error("vptc_dda_trace_csv: " + err); return VPTC_ERR_BAD_GRID; }
+    } catch (const std::exception& e) { set_global_error(std::string("vptc_dda_trace_csv: ") + e.what()); return VPTC_ERR_IO; }
+    return VPTC_OK;
+}
+// The same for an explicit world-space ray (the reference's log_dda_trace takes a vpt::Ray).
+int vptc_dda_trace_ray_csv(const void* density_grid, size_t density_bytes, const float origin_xyz[3], const float direction_xyz[3], const char* csv_path, size_t* n_rows)
+{
+    if (n_rows) *n_rows = 0;
+    if (!density_grid || !origin_xyz || !direction_xyz || !csv_path) { set_global_error("vptc_dda_trace_ray_csv: null argument"); return VPTC_ERR_INVALID_ARGUMENT; }
+    try {
+        const std::string err = vpt_host::write_dda_trace(density_grid, density_bytes, origin_xyz, direction_xyz, csv_path, n_rows);
+        if (!err.empty()) { set_global_error("vptc_dda_trace_ray_csv: " + err); return VPTC_ERR_BAD_GRID; }
+    } catch (const std::exception& e) { set_global_error(std::string("vptc_dda_trace_ray_csv: ") + e.what()); return VPTC_ERR_IO; }
     return VPTC_OK;
 }
 

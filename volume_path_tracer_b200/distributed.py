@@ -27,16 +27,18 @@ def shard_waves(first_wave: int, n_waves: int, rank: int, world: int) -> Tuple[i
     return first_wave + rank, count, world
 
 
-def shard_tile_rows(scene, rank: int, world: int) -> Tuple[int, int, int, int]:
-    """Tile-stripe partition for low spp / large frames (the reference numbers tiles row-major, src/tile_provider.cpp:95-105): rank r
-    takes a contiguous block of tile ROWS, i.e. one contiguous band of film rows. -> (tile_begin, tile_count, y0, y1) for
-    vptc_job_range / Renderer.run_device_range; disjoint pixels across ranks, so the films are GATHERED, not summed."""
+def shard_tile_rows(scene, rank: int, world: int):
+    """Tile-stripe partition for low spp / large frames (the reference numbers tiles row-major, src/tile_provider.cpp:95-105): rank r takes
+    the ROWS of tiles r, r + world, r + 2*world, ... — interleaved, so that the ranks share the expensive part of the frame evenly (contiguous
+    halves of the 4K cloud differed by 70 % in cost). -> (tile_begin, tile_count, tile_row_stride, rows) for vptc_job_range /
+    Renderer.run_device_range, `rows` = the film rows this rank renders (a torch-indexable list of slices, one per row of tiles).
+    Disjoint pixels across ranks, so the films are GATHERED, not summed."""
     if world < 1 or not (0 <= rank < world):
         raise ValueError("bad rank/world")
     W, H, tw, th = scene.width, scene.height, int(scene.tile_size[0]), int(scene.tile_size[1])
     ntx, nty = -(-W // tw), -(-H // th)
-    r0, r1 = nty * rank // world, nty * (rank + 1) // world
-    return r0 * ntx, (r1 - r0) * ntx, min(H, r0 * th), min(H, r1 * th)
+    mine = list(range(rank, nty, world))
+    return rank * ntx, len(mine) * ntx, world, [slice(r * th, min(H, (r + 1) * th)) for r in mine]
 
 
 def reduce_film(film, dst: int = 0):
@@ -48,23 +50,27 @@ def reduce_film(film, dst: int = 0):
 
 
 def gather_film_stripes(film, scene, rank: int, world: int, dst: int = 0):
-    """Tile-stripe sharding: every rank's band of film rows (shard_tile_rows) is gathered into rank `dst`'s film with ONE collective
-    (NCCL gather over NVLink on GPUs, gloo in the CPU tests). Bands differ by at most one tile row: padded to the tallest for the call."""
+    """Tile-stripe sharding: every rank's bands of film rows (shard_tile_rows) are gathered into rank `dst`'s film with ONE collective
+    (NCCL gather over NVLink on GPUs, gloo in the CPU tests). Ranks differ by at most one row of tiles: padded to the largest for the call."""
     import torch
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
         return film
-    bands = [shard_tile_rows(scene, r, world)[2:] for r in range(world)]
-    rows = max(y1 - y0 for y0, y1 in bands)
-    y0, y1 = bands[rank]
+
+    def row_index(r):
+        sl = shard_tile_rows(scene, r, world)[3]
+        return torch.cat([torch.arange(s.start, s.stop) for s in sl]) if sl else torch.zeros(0, dtype=torch.long)
+    idx = [row_index(r) for r in range(world)]
+    rows = max(len(i) for i in idx)
     send = torch.zeros((rows,) + tuple(film.shape[1:]), dtype=film.dtype, device=film.device)
-    send[: y1 - y0] = film[y0:y1]
+    mine = idx[rank].to(film.device)
+    send[: len(mine)] = film.index_select(0, mine)
     recv = [torch.empty_like(send) for _ in range(world)] if rank == dst else None
     dist.gather(send, recv, dst=dst)
     if rank == dst:
-        for r, (a, b) in enumerate(bands):
-            if r != dst and b > a:
-                film[a:b] = recv[r][: b - a]
+        for r in range(world):
+            if r != dst and len(idx[r]):
+                film.index_copy_(0, idx[r].to(film.device), recv[r][: len(idx[r])])
     return film
 
 
