@@ -242,6 +242,16 @@ VPTC_API int vptc_blackbody(vptc_ctx* ctx, const float* temps_k, size_t n, float
  * sRGB OETF -> clamp -> *255 -> truncate, on the device, byte-identical to the host code (glibc-exact powf). Host film in, host RGB8 out. */
 VPTC_API int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8);
 
+/* vptc_film_to_image without any allocation. NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same kernel, same bytes out;
+ * the device staging (film in, RGB8 out) is a file-scope static __device__ array of VPTC_STATIC_IMAGE_MAX_PIXELS * 19 bytes (38 MiB) that
+ * every GPU which loads the library holds until the process exits. The call makes no cudaMalloc / cudaFree / allocating library call.
+ * width * height > VPTC_STATIC_IMAGE_MAX_PIXELS (1920 x 1080 fits) -> VPTC_ERR_INVALID_ARGUMENT, with the limit in vptc_last_error.
+ * All calls on one GPU share the array (it keeps the previous call's contents; the call overwrites what it reads, nothing needs clearing):
+ * calls that overlap on the same GPU — two host threads, two contexts on one device — race; serialise them. */
+#define VPTC_STATIC_IMAGE_MAX_PIXELS (1u << 21)
+VPTC_API int vptc_film_to_image_static(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8);
+
 /* ---- host-side helpers (no GPU needed) ----
  * Everything from here on is plain host code. It is exported by libvptcuda.so and, without any CUDA dependency, by libvpthost.so (the same
  * objects linked alone), so that tools which only need the scene reader, the .nvdb reader/writer, the procedural volumes or the PNG writer —

@@ -100,7 +100,7 @@ class VptError(RuntimeError):
 
 EXPORTS = [
     "vptc_create", "vptc_destroy", "vptc_last_error", "vptc_set_volume", "vptc_render", "vptc_render_device", "vptc_render_device_range", "vptc_render_device_async", "vptc_render_async", "vptc_wait", "vptc_render_adaptive", "vptc_last_render_ms", "vptc_device_volume_bytes",
-    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_blackbody",
+    "vptc_get_counters", "vptc_enable_counters", "vptc_set_kernel_variant", "vptc_trace_jobs", "vptc_trace_segments", "vptc_trace_pixel_csv", "vptc_trace_path_log", "vptc_sample_grid", "vptc_film_to_image", "vptc_film_to_image_static", "vptc_blackbody",
     "vptc_scene_from_json_file", "vptc_scene_from_json", "vptc_nvdb_read_grid", "vptc_nvdb_write_grids", "vptc_free",
     "vptc_synth_volume", "vptc_write_png", "vptc_film_save", "vptc_film_load", "vptc_version", "vptc_host_last_error", "vptc_dda_trace_csv", "vptc_dda_trace_ray_csv",
     "vptc_group_create", "vptc_group_destroy", "vptc_group_last_error", "vptc_group_size", "vptc_group_peer_mapped", "vptc_group_set_volume", "vptc_group_render",
@@ -192,6 +192,7 @@ def lib() -> C.CDLL:
     L.vptc_trace_path_log.argtypes = [vp, C.POINTER(Scene), C.c_uint64, C.c_int64, C.c_int64, vp, sz, C.POINTER(sz)]
     L.vptc_sample_grid.argtypes = [vp, C.c_int, vp, sz, vp, vp, vp]
     L.vptc_film_to_image.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
+    L.vptc_film_to_image_static.argtypes = [vp, vp, C.c_int64, C.c_int64, vp]
     L.vptc_blackbody.argtypes = [vp, vp, sz, vp]
     _declare_host(L)
     L.vptc_group_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
@@ -448,8 +449,16 @@ class Renderer:
         _check(lib().vptc_film_to_image(self._ctx, _ptr(film), film.shape[1], film.shape[0], _ptr(rgb)), self._ctx)
         return rgb
 
+    def film_to_image_static(self, film: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """vptc_film_to_image_static: no allocation on the device (static scratch, at most STATIC_IMAGE_MAX_PIXELS pixels)."""
+        film = np.ascontiguousarray(film, dtype=np.float32)
+        rgb = out if out is not None else np.zeros(film.shape[:2] + (3,), np.uint8)
+        _check(lib().vptc_film_to_image_static(self._ctx, _ptr(film), film.shape[1], film.shape[0], _ptr(rgb)), self._ctx)
+        return rgb
+
 
 SHARD_WAVES, SHARD_TILES = 0, 1
+STATIC_IMAGE_MAX_PIXELS = 1 << 21  # VPTC_STATIC_IMAGE_MAX_PIXELS (include/vptc.h)
 
 
 class Group:

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <exception>
 #include <memory>
+#include <mutex>
 #include <chrono>
 #include <string>
 #include <thread>
@@ -840,6 +841,59 @@ int vptc_film_to_image(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cleanup();
     if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image: ") + cudaGetErrorString(e));
+    return VPTC_OK;
+}
+
+// ---- vptc_film_to_image_static: the same resolve kernel, staging in a file-scope device array instead of cudaMalloc'ed buffers ----
+// For callers that may not allocate (CUDA graph capture around them, serving loops, harnesses that forbid cudaMalloc). No counterpart in the
+// reference. The array lives in every GPU that loads this library until the process exits:
+// VPTC_STATIC_IMAGE_MAX_PIXELS * (16 + 3) bytes = 38 MiB. Every call on a device shares it (and it keeps the last call's contents: the
+// call overwrites the n pixels it uses before reading them, nothing has to start at zero), so calls that overlap on one GPU race.
+} // extern "C" (the array and its helper have C++ linkage)
+static __device__ __align__(256) unsigned char g_static_image_scratch[size_t(VPTC_STATIC_IMAGE_MAX_PIXELS) * 19];
+
+namespace {
+// In host code `g_static_image_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, asked once per device with
+// that device current.
+constexpr int kMaxStaticDevices = 256;
+unsigned char* g_static_image_ptr[kMaxStaticDevices] = {};
+std::mutex g_static_image_mutex;
+cudaError_t static_image_scratch(int device, unsigned char** out)
+{
+    if (device < 0 || device >= kMaxStaticDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_image_mutex);
+    if (!g_static_image_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_image_scratch); // the current device's instance of the array
+        if (e != cudaSuccess) return e;
+        g_static_image_ptr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_image_ptr[device];
+    return cudaSuccess;
+}
+} // namespace
+extern "C" {
+
+int vptc_film_to_image_static(vptc_ctx* ctx, const float* film_xyzw, int64_t width, int64_t height, uint8_t* rgb8)
+{
+    if (!ctx) return fail(nullptr, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image_static: ctx is null");
+    if (!film_xyzw || !rgb8 || width <= 0 || height <= 0)
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image_static: null pointer or a side < 1");
+    if (width > int64_t(VPTC_STATIC_IMAGE_MAX_PIXELS) || height > int64_t(VPTC_STATIC_IMAGE_MAX_PIXELS) || width * height > int64_t(VPTC_STATIC_IMAGE_MAX_PIXELS))
+        return fail(ctx, VPTC_ERR_INVALID_ARGUMENT, "vptc_film_to_image_static: " + std::to_string(width) + " x " + std::to_string(height) + " pixels exceed the static scratch of VPTC_STATIC_IMAGE_MAX_PIXELS = " +
+                                                        std::to_string(VPTC_STATIC_IMAGE_MAX_PIXELS) + " pixels; use vptc_film_to_image");
+    CU(cudaSetDevice(ctx->device));
+    unsigned char* scratch = nullptr;
+    cudaError_t e = static_image_scratch(ctx->device, &scratch);
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    const size_t n = size_t(width) * size_t(height);
+    float* d_f = reinterpret_cast<float*>(scratch);                                     // n float4 pixels, overwritten below
+    uint8_t* d_rgb = scratch + size_t(VPTC_STATIC_IMAGE_MAX_PIXELS) * 16;               // n RGB8 pixels, every byte written by the kernel
+    e = cudaMemcpyAsync(d_f, film_xyzw, n * 16, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_resolve(d_f, n, d_rgb, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb8, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return fail(ctx, VPTC_ERR_CUDA, std::string("vptc_film_to_image_static: ") + cudaGetErrorString(e));
     return VPTC_OK;
 }
 
