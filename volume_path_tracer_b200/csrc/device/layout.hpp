@@ -30,7 +30,32 @@ constexpr uint32_t SLOT_INDEX_MASK = 0x7fffffffu;
 struct Slot { uint32_t code; float majorant; }; // 8 bytes, loaded as one 64-bit word
 
 constexpr int BRICK_EDGE = 9;
-constexpr int BRICK_STRIDE = 736; // floats; >= 9^3 = 729
+// Fetch-layout switch (profiles/r02_fetch_layout.txt). 0, the default: rows of 9 floats, a trilinear request = 8 scalar loads touching
+// 4 rows. 1: every (x, y) row stores its 8 OVERLAPPING z-pairs {v[z], v[z+1]}, z = 0..7, as 8-byte-aligned float2 — a request is
+// 4 x LDG.64 that never straddle a 32-byte sector, at 1.76x the brick bytes. 2: see below.
+#ifndef VPT_BRICK_PAIRS
+#define VPT_BRICK_PAIRS 0
+#endif
+#if defined(__CUDACC__)
+#define VPT_LAYOUT_HD __host__ __device__
+#else
+#define VPT_LAYOUT_HD
+#endif
+#if VPT_BRICK_PAIRS == 2
+// 2: every voxel of the leaf stores its whole 2x2x2 stencil {v000, v001, v010, v011, v100, v101, v110, v111} as one 32-byte-aligned
+// group — a trilinear request is ONE sector (2 x LDG.128), at 5.6x the brick bytes (no apron: the +1 neighbours are folded in at bake time).
+constexpr int BRICK_ROW = 64;                 // floats per (x, y) row: 8 voxels x 8 corners
+constexpr int BRICK_STRIDE = 8 * 8 * 8 * 8;   // 4096 floats = 16 KiB = 512 sectors
+VPT_LAYOUT_HD constexpr int brick_offset(int x, int y, int z) { return ((x * 8 + y) * 8 + z) * 8; } // x, y, z in 0..7: the voxel's own value comes first
+#elif VPT_BRICK_PAIRS
+constexpr int BRICK_ROW = 16;                 // floats per (x, y) row: 8 float2
+constexpr int BRICK_STRIDE = 9 * 9 * 16;      // 1296 floats = 5184 B = 162 sectors
+VPT_LAYOUT_HD constexpr int brick_offset(int x, int y, int z) { return (x * 9 + y) * BRICK_ROW + 2 * z; } // x, y in 0..8, z in 0..7: first float of the pair
+#else
+constexpr int BRICK_ROW = 9;
+constexpr int BRICK_STRIDE = 736;             // floats; >= 9^3 = 729 (2944 B = 92 sectors of 32 B)
+VPT_LAYOUT_HD constexpr int brick_offset(int x, int y, int z) { return (x * 9 + y) * BRICK_ROW + z; }       // x, y, z in 0..8
+#endif
 
 struct GridDev {
     // NanoVDB Map, float members verbatim (NV/NanoVDB.h:1375-1381)

@@ -99,7 +99,28 @@ __device__ __forceinline__ float value_at(const GridDev& G, int x, int y, int z)
     if (c & CELL_KIND_TILE) return __ldg(&G.tile_value[c & CELL_INDEX_MASK]);
     const Slot s = load_slot(G, slot_index(c, x, y, z));
     if (s.code & SLOT_KIND_TILE) return __ldg(&G.tile_value[s.code & SLOT_INDEX_MASK]);
-    return __ldg(&G.bricks[size_t(s.code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7)]);
+    return __ldg(&G.bricks[size_t(s.code) * BRICK_STRIDE + brick_offset(x & 7, y & 7, z & 7)]);
+}
+// The 8 corners of the trilinear stencil whose base voxel (x, y, z) lies in brick `code`: all inside the 9^3 apron brick.
+__device__ __forceinline__ void brick_corners(const GridDev& G, uint32_t code, int x, int y, int z, float& v000, float& v001, float& v010, float& v011,
+                                              float& v100, float& v101, float& v110, float& v111)
+{
+    const float* b = G.bricks + size_t(code) * BRICK_STRIDE + brick_offset(x & 7, y & 7, z & 7);
+#if VPT_BRICK_PAIRS == 2
+    const float4 lo = __ldg(reinterpret_cast<const float4*>(b)), hi = __ldg(reinterpret_cast<const float4*>(b) + 1);
+    v000 = lo.x; v001 = lo.y; v010 = lo.z; v011 = lo.w;
+    v100 = hi.x; v101 = hi.y; v110 = hi.z; v111 = hi.w;
+#elif VPT_BRICK_PAIRS
+    const float2 p00 = __ldg(reinterpret_cast<const float2*>(b)), p01 = __ldg(reinterpret_cast<const float2*>(b + BRICK_ROW));
+    const float2 p10 = __ldg(reinterpret_cast<const float2*>(b + 9 * BRICK_ROW)), p11 = __ldg(reinterpret_cast<const float2*>(b + 10 * BRICK_ROW));
+    v000 = p00.x; v001 = p00.y; v010 = p01.x; v011 = p01.y;
+    v100 = p10.x; v101 = p10.y; v110 = p11.x; v111 = p11.y;
+#else
+    v000 = __ldg(b);      v001 = __ldg(b + 1);
+    v010 = __ldg(b + 9);  v011 = __ldg(b + 10);
+    v100 = __ldg(b + 81); v101 = __ldg(b + 82);
+    v110 = __ldg(b + 90); v111 = __ldg(b + 91);
+#endif
 }
 // SampleFromVoxels<Acc,1>::operator()(Vec3f)   NV/math/SampleFromVoxels.h:62-69,202-242
 __device__ __forceinline__ float trilinear(const GridDev& G, float px, float py, float pz)
@@ -113,11 +134,7 @@ __device__ __forceinline__ float trilinear(const GridDev& G, float px, float py,
     if (!(c & CELL_KIND_TILE)) {
         const Slot s = load_slot(G, slot_index(c, x, y, z));
         if (!(s.code & SLOT_KIND_TILE)) { // base voxel in a leaf: the 9^3 apron brick holds all 8 corners
-            const float* b = G.bricks + size_t(s.code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7);
-            v000 = __ldg(b);      v001 = __ldg(b + 1);
-            v010 = __ldg(b + 9);  v011 = __ldg(b + 10);
-            v100 = __ldg(b + 81); v101 = __ldg(b + 82);
-            v110 = __ldg(b + 90); v111 = __ldg(b + 91);
+            brick_corners(G, s.code, x, y, z, v000, v001, v010, v011, v100, v101, v110, v111);
             fast = true;
         }
     }

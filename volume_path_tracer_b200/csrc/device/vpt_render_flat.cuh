@@ -75,11 +75,7 @@ __device__ __forceinline__ float trilinear_cached(const GridDev& G, CellCache& c
     if (!(c & CELL_KIND_TILE)) {
         const Slot s = load_slot(G, slot_index(c, x, y, z));
         if (!(s.code & SLOT_KIND_TILE)) {
-            const float* b = G.bricks + size_t(s.code) * BRICK_STRIDE + ((x & 7) * 9 + (y & 7)) * 9 + (z & 7);
-            v000 = __ldg(b);      v001 = __ldg(b + 1);
-            v010 = __ldg(b + 9);  v011 = __ldg(b + 10);
-            v100 = __ldg(b + 81); v101 = __ldg(b + 82);
-            v110 = __ldg(b + 90); v111 = __ldg(b + 91);
+            brick_corners(G, s.code, x, y, z, v000, v001, v010, v011, v100, v101, v110, v111);
             fast = true;
         }
     }

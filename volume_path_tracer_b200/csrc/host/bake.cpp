@@ -7,9 +7,11 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
+#include <string>
 #include <thread>
 
 #include "nvdb_build.hpp" // check_grid
@@ -219,6 +221,27 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         }
     }
 
+    // ---- brick order: leaf-array order (NanoVDB's breadth-first order: leaves of one lower node are contiguous, z fastest), or, for the
+    // fetch-layout experiment (VPT_BAKE_BRICK_ORDER=morton, profiles/r02_fetch_layout.txt), Morton order of the leaf origins ----
+    std::vector<uint32_t> brick_of(nLeaf);
+    for (size_t i = 0; i < nLeaf; ++i) brick_of[i] = uint32_t(i);
+    if (const char* ord = std::getenv("VPT_BAKE_BRICK_ORDER"); ord && std::string(ord) == "morton" && nLeaf > 1) {
+        auto spread = [](uint64_t v) { // 21 bits -> every third bit
+            v &= 0x1fffffull;
+            v = (v | v << 32) & 0x1f00000000ffffull; v = (v | v << 16) & 0x1f0000ff0000ffull; v = (v | v << 8) & 0x100f00f00f00f00full;
+            v = (v | v << 4) & 0x10c30c30c30c30c3ull; v = (v | v << 2) & 0x1249249249249249ull;
+            return v;
+        };
+        std::vector<std::pair<uint64_t, uint32_t>> keyed(nLeaf);
+        for (size_t i = 0; i < nLeaf; ++i) {
+            const LeafData* lf = tv.leaf0 + i;
+            const uint64_t x = uint64_t(uint32_t(lf->bboxMin[0] >> 3) + (1u << 20)), y = uint64_t(uint32_t(lf->bboxMin[1] >> 3) + (1u << 20)), z = uint64_t(uint32_t(lf->bboxMin[2] >> 3) + (1u << 20));
+            keyed[i] = {spread(x) << 2 | spread(y) << 1 | spread(z), uint32_t(i)};
+        }
+        std::sort(keyed.begin(), keyed.end());
+        for (size_t r = 0; r < nLeaf; ++r) brick_of[keyed[r].second] = uint32_t(r);
+    }
+
     // ---- lower slots (codes now, majorants after the patch) ----
     out.slots.assign(nLower * 4096 * 2, 0u);
     for (size_t li = 0; li < nLower; ++li) {
@@ -227,7 +250,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
             uint32_t code; float maj;
             if (mask_on(l->childMask, n)) {
                 const LeafData* lf = tv.leaf_of(l, n);
-                code = uint32_t(lf - tv.leaf0);
+                code = brick_of[size_t(lf - tv.leaf0)];
                 maj = lf->maximum; // patched below
             } else {
                 const uint32_t ti = tile_of(l->table[n].value, mask_on(l->valueMask, n));
@@ -245,11 +268,24 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
     parallel_for(nLeaf, [&](size_t bi) {
         const LeafData* lf = tv.leaf0 + bi;
         const int32_t o[3] = {lf->bboxMin[0] & ~7, lf->bboxMin[1] & ~7, lf->bboxMin[2] & ~7};
-        float* dst = &out.bricks[bi * size_t(BRICK_STRIDE)];
+        float dst[729]; // the 9^3 apron brick, x-major; laid out into the device format below
         for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) for (int k = 0; k < 9; ++k) {
             const bool core = i < 8 && j < 8 && k < 8;
             dst[(i * 9 + j) * 9 + k] = core ? lf->values[(i << 6) | (j << 3) | k] : tv.value(o[0] + i, o[1] + j, o[2] + k);
         }
+        float* dev = &out.bricks[size_t(brick_of[bi]) * size_t(BRICK_STRIDE)];
+#if VPT_BRICK_PAIRS == 2
+        for (int i = 0; i < 8; ++i) for (int j = 0; j < 8; ++j) for (int k = 0; k < 8; ++k)
+            for (int c = 0; c < 8; ++c) dev[brick_offset(i, j, k) + c] = dst[((i + (c >> 2)) * 9 + (j + ((c >> 1) & 1))) * 9 + (k + (c & 1))];
+#else
+        for (int i = 0; i < 9; ++i) for (int j = 0; j < 9; ++j) {
+#if VPT_BRICK_PAIRS
+            for (int k = 0; k < 8; ++k) { dev[brick_offset(i, j, k)] = dst[(i * 9 + j) * 9 + k]; dev[brick_offset(i, j, k) + 1] = dst[(i * 9 + j) * 9 + k + 1]; }
+#else
+            for (int k = 0; k < 9; ++k) dev[brick_offset(i, j, k)] = dst[(i * 9 + j) * 9 + k];
+#endif
+        }
+#endif
         float m = lf->maximum; // stats over ACTIVE voxels only (NV/tools/GridStats.h:716-730)
         if (patch_majorants) {
             // max over the 1-voxel shell [o-1, o+8]^3 \ leaf, read through getValue (volume.cpp:128-156)
@@ -263,9 +299,11 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         }
         out.brick_max[bi] = m;
     });
+    std::vector<float> max_by_brick(nLeaf);
+    for (size_t i = 0; i < nLeaf; ++i) max_by_brick[brick_of[i]] = out.brick_max[i];
     for (size_t e = 0; e < nLower * 4096; ++e) {
         const uint32_t code = out.slots[e * 2];
-        if (!(code & SLOT_KIND_TILE)) std::memcpy(&out.slots[e * 2 + 1], &out.brick_max[code], 4);
+        if (!(code & SLOT_KIND_TILE)) std::memcpy(&out.slots[e * 2 + 1], &max_by_brick[code], 4);
     }
     h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
     h.background_tile = 0;

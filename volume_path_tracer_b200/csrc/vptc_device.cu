@@ -384,6 +384,8 @@ int vptc_create(vptc_ctx** out, int device)
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     ctx->num_sms = prop.multiProcessorCount;
+    if (const char* v = std::getenv("VPT_L2_FETCH_GRANULARITY")) // 32 / 64 / 128 bytes (profiles/r02_fetch_layout.txt); a hint, device-wide
+        CU(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::max(32, std::atoi(v)))));
     CU(cudaStreamCreate(&ctx->stream)); // blocking stream: ordered after work on the legacy default stream (torch)
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
