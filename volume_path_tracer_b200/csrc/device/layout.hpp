@@ -57,6 +57,21 @@ constexpr int BRICK_STRIDE = 736;             // floats; >= 9^3 = 729 (2944 B = 
 VPT_LAYOUT_HD constexpr int brick_offset(int x, int y, int z) { return (x * 9 + y) * BRICK_ROW + z; }       // x, y, z in 0..8
 #endif
 
+// Majorant-table switch (profiles/r02_kernel_ab.txt). 0, the default: the HDDA reads the majorant out of the 8-byte {code, majorant} slot.
+// 1: a second table of 4-byte majorants in the same order (x << 8 | y << 4 | z inside a lower node): twice the entries per line.
+// 2: that table in 2x4x4 blocks per 128-byte line, so that a step to a neighbouring leaf in ANY axis mostly stays in the line.
+#ifndef VPT_SPLIT_MAJ
+#define VPT_SPLIT_MAJ 0
+#endif
+VPT_LAYOUT_HD constexpr uint32_t maj_index(uint32_t xs, uint32_t ys, uint32_t zs) // leaf position inside its lower node, 0..15 each
+{
+#if VPT_SPLIT_MAJ == 2
+    return (xs >> 2) << 10 | (ys >> 2) << 8 | (zs >> 2) << 6 | (xs & 3u) << 4 | (ys & 3u) << 2 | (zs & 3u);
+#else
+    return xs << 8 | ys << 4 | zs;
+#endif
+}
+
 struct GridDev {
     // NanoVDB Map, float members verbatim (NV/NanoVDB.h:1375-1381)
     float mat[9], invMat[9], vec[3];
@@ -70,6 +85,7 @@ struct GridDev {
     const float* tile_majorant;       // [nTiles] active ? value : 0        (volume.cpp:28-34)
     const float* bricks;              // [nBricks * BRICK_STRIDE]
     uint32_t n_lower, n_bricks, n_tiles, pad_;
+    const float* slot_majorant;       // [nLower * 4096] the slots' majorants alone, maj_index order (VPT_SPLIT_MAJ builds; else null)
 };
 
 // vpt::Configuration flattened to what the kernels read, plus host-precomputed constants.

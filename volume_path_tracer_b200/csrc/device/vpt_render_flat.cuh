@@ -48,7 +48,11 @@ __device__ __forceinline__ float majorant_cached(const GridDev& G, CellCache& cc
 {
     const uint32_t c = cell_code_cached(G, cc, x, y, z);
     if (c & CELL_KIND_TILE) return __ldg(&G.tile_majorant[c & CELL_INDEX_MASK]);
+#if VPT_SPLIT_MAJ
+    return __ldg(&G.slot_majorant[(c & CELL_INDEX_MASK) * 4096u + maj_index(uint32_t(x & 127) >> 3, uint32_t(y & 127) >> 3, uint32_t(z & 127) >> 3)]);
+#else
     return load_slot(G, slot_index(c, x, y, z)).majorant;
+#endif
 }
 // Base voxel in a tile / background (its corners may still reach into leaves): 8 full getValue descents. Rare, and
 // deliberately NOT inlined — the render loop has to stay small for the instruction cache.

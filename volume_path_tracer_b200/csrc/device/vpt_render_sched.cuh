@@ -43,6 +43,10 @@ namespace vptd {
 #ifndef VPT_DEFER_INF
 #define VPT_DEFER_INF 0 // a ray that leaves the volume only marks the pixel; the infinite light is added where the pixel is closed (no cold-state traffic in HOT)
 #endif
+#ifndef VPT_LOOKAHEAD
+#define VPT_LOOKAHEAD 0 // the HDDA runs ONE STEP AHEAD of the segment logic: a pass first takes the pair (t0, majorant) whose load the previous pass issued, steps again and
+                        // issues the next load, and only then consumes the pair — a whole pass between a slot load and its use (profiles/r02_kernel_ab.txt)
+#endif
 enum : int { ST_SETUP = 0, ST_HOT = 1, ST_EVAL = 2, ST_EXIT = 3 };
 enum : int { PH_NEXT_PIXEL_INF = 5 }; // NEXT_PIXEL for a path that escaped to the infinite light (VPT_DEFER_INF)
 
@@ -72,6 +76,25 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     enum : int { M_STEP = 0, M_PEND = 1, M_DRAW = 2 }; // marching: step next / majorant fetch in flight; drawing in a closed segment
     int mode = M_STEP;
     float pend_u = 0.0f;
+#if VPT_LOOKAHEAD
+    float c_t0 = 0.0f, c_maj = 0.0f; // the pair the segment logic is looking at; (m.t0, m.majorant) is the HDDA's, one step further
+#define VPT_CUR_T0 c_t0
+#define VPT_CUR_MAJ c_maj
+#else
+#define VPT_CUR_T0 m.t0
+#define VPT_CUR_MAJ m.majorant
+#endif
+    // one HDDA step with the next node's majorant fetch issued   volume.cpp:53-59
+#define VPT_HDDA_ADVANCE()                                                                                                              \
+    do {                                                                                                                                \
+        if (!hdda_step_bf(m)) m.majorant = __int_as_float(0x7fc00000);                                                                  \
+        else {                                                                                                                          \
+            const V3 p_ = m.at(m.t0 + 1.0001f);                                                                                         \
+            hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p_.x)), int(floorf(p_.y)), int(floorf(p_.z)))));              \
+            m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);                                                                      \
+            if (COUNT && !VPT_LOOKAHEAD) ++st.majorant_fetches;                                                                         \
+        }                                                                                                                               \
+    } while (0)
     bool shadow = false, pixel_open = false;
     int stage = ST_SETUP, sub = PH_NEXT_PIXEL;
     unsigned long long j = 0;
@@ -254,7 +277,13 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                     const RayDir rdir = shadow ? shadow_dir : make_ray_dir(G, rd);
                     if (flat_begin_ray_dir<COUNT>(m, G, cc, CLD3(C_POS), rdir, ray_done, st)) {
                         if (ray_done) VPT_RAY_FINISHED();
-                        else { stage = ST_HOT; mode = M_STEP; }
+                        else {
+                            stage = ST_HOT; mode = M_STEP;
+#if VPT_LOOKAHEAD
+                            c_t0 = m.t0; c_maj = m.majorant; // the first pair is current; the HDDA goes one step ahead right here
+                            VPT_HDDA_ADVANCE();
+#endif
+                        }
                     } else if (shadow) sub = PH_AFTER_SHADOW; // the shadow ray misses the volume: T stays 1
                     else VPT_ADD_INF_LIGHT(); // the camera / bounce ray misses the volume
                 }
@@ -277,13 +306,21 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
 #else
 #define HOT_FINISH() VPT_RAY_FINISHED()
 #endif
+#if VPT_LOOKAHEAD
+            if (mode == M_STEP) { // the pair fetched a pass ago becomes current (its load is waited for HERE), and the HDDA moves on at once
+                c_t0 = m.t0; c_maj = m.majorant;
+                if (COUNT && c_t0 <= m.t1) ++st.majorant_fetches; // counted when consumed: the reference never fetches the look-ahead node of a ray that ends first
+                if (m.t0 <= m.t1) VPT_HDDA_ADVANCE();             // a step that left the ray is the last one
+                mode = M_PEND;
+            }
+#endif
             if (mode == M_PEND) { // RayMajorantIterator::next after the step: volume.cpp:60-70
                 mode = M_STEP;
-                if (m.majorant != m.seg_dmaj) {                 // NaN after a failed step: the segment closes at t1
-                    m.seg_t1 = fminf(m.t0, m.t1);               // t0 on a successful step (t0 <= t1), t1 when the step left the ray
+                if (VPT_CUR_MAJ != m.seg_dmaj) {                 // NaN after a failed step: the segment closes at t1
+                    m.seg_t1 = fminf(VPT_CUR_T0, m.t1);               // t0 on a successful step (t0 <= t1), t1 when the step left the ray
                     if (m.seg_dmaj > 0.0f) mode = M_DRAW;
-                    else if (m.t0 >= m.t1) HOT_FINISH();               // empty segment dropped, iterator.next() -> nullopt
-                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; } // ... or the next segment starts
+                    else if (VPT_CUR_T0 >= m.t1) HOT_FINISH();               // empty segment dropped, iterator.next() -> nullopt
+                    else { m.seg_t0 = VPT_CUR_T0; m.seg_dmaj = VPT_CUR_MAJ; } // ... or the next segment starts
                 }
             }
             if (mode == M_DRAW && stage == ST_HOT) { // MajorantTransmittanceSampler::next, the draw   majorant_transmittance_sampler.cpp:41-47
@@ -306,24 +343,20 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 if (m.seg_t0 + dtp > m.seg_t1 + (1.0e-5f * fabsf(m.seg_t1) + 1.0e-5f)) { // certainly t >= seg.t1: segment dropped
 #endif
                     mode = M_STEP;
-                    if (m.t0 >= m.t1) HOT_FINISH();
-                    else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
+                    if (VPT_CUR_T0 >= m.t1) HOT_FINISH();
+                    else { m.seg_t0 = VPT_CUR_T0; m.seg_dmaj = VPT_CUR_MAJ; }
                 } else stage = ST_EVAL;
             }
 #if VPT_HOT_SINGLE_FINISH
             if (fin) VPT_RAY_FINISHED();
 #endif
 #undef HOT_FINISH
+#if !VPT_LOOKAHEAD
             if (mode == M_STEP && stage == ST_HOT) { // one HDDA step, majorant fetch issued   volume.cpp:53-59
-                if (!hdda_step_bf(m)) m.majorant = __int_as_float(0x7fc00000);
-                else {
-                    const V3 p = m.at(m.t0 + 1.0001f);
-                    hdda_update(m, dim_of_code(cell_code_cached(G, cc, int(floorf(p.x)), int(floorf(p.y)), int(floorf(p.z)))));
-                    m.majorant = majorant_cached(G, cc, m.vx, m.vy, m.vz);
-                    if (COUNT) ++st.majorant_fetches;
-                }
+                VPT_HDDA_ADVANCE();
                 mode = M_PEND;
             }
+#endif
         }
         // ------------------------------------------------------------ EVAL: trilinear density + collision   worker.cpp:68-84,148-188
         if (run_eval && stage == ST_EVAL) {
@@ -341,8 +374,8 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                 if (density > 0.0f) pos_idx = p;
             } else { // overshoot after all: segment dropped, iterator.next()
                 mode = M_STEP;
-                if (m.t0 >= m.t1) VPT_RAY_FINISHED();
-                else { m.seg_t0 = m.t0; m.seg_dmaj = m.majorant; }
+                if (VPT_CUR_T0 >= m.t1) VPT_RAY_FINISHED();
+                else { m.seg_t0 = VPT_CUR_T0; m.seg_dmaj = VPT_CUR_MAJ; }
             }
             if (density > 0.0f) {
                 if (shadow) { // ratio tracking + Russian roulette
@@ -401,6 +434,9 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
         }
     }
 #undef VPT_RAY_FINISHED
+#undef VPT_HDDA_ADVANCE
+#undef VPT_CUR_T0
+#undef VPT_CUR_MAJ
 #undef VPT_ADD_INF_LIGHT
 #undef VPT_EVENT
 #undef CLDF

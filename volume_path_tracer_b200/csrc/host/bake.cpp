@@ -305,6 +305,12 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         const uint32_t code = out.slots[e * 2];
         if (!(code & SLOT_KIND_TILE)) std::memcpy(&out.slots[e * 2 + 1], &max_by_brick[code], 4);
     }
+#if VPT_SPLIT_MAJ
+    out.slot_majorant.assign(nLower * 4096, 0.0f);
+    for (size_t li = 0; li < nLower; ++li)
+        for (uint32_t n = 0; n < 4096; ++n)
+            std::memcpy(&out.slot_majorant[li * 4096 + maj_index(n >> 8, (n >> 4) & 15u, n & 15u)], &out.slots[(li * 4096 + n) * 2 + 1], 4);
+#endif
     h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
     h.background_tile = 0;
 }

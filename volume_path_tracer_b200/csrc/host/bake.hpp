@@ -14,8 +14,9 @@ struct BakedGrid {
     std::vector<uint32_t> slots;      // 2 x uint32 per slot: {code, majorant bits}
     std::vector<float> tile_value, tile_majorant;
     std::vector<float> bricks;        // n_bricks * BRICK_STRIDE
+    std::vector<float> slot_majorant; // VPT_SPLIT_MAJ builds: the slots' majorants alone, maj_index order (else empty)
     std::vector<float> brick_max;     // patched leaf maxima, leaf-array order (also folded into `slots`)
-    size_t device_bytes() const { return cells.size() * 4 + slots.size() * 4 + (tile_value.size() + tile_majorant.size() + bricks.size()) * 4; }
+    size_t device_bytes() const { return cells.size() * 4 + slots.size() * 4 + slot_majorant.size() * 4 + (tile_value.size() + tile_majorant.size() + bricks.size()) * 4; }
 };
 
 // Throws std::runtime_error on a malformed grid. patch_majorants = apply fix_majorants_for_interpolation

@@ -25,12 +25,12 @@ using namespace vptd;
 
 struct DeviceGrid {
     GridDev dev{};
-    void *cells = nullptr, *slots = nullptr, *tile_value = nullptr, *tile_majorant = nullptr, *bricks = nullptr;
+    void *cells = nullptr, *slots = nullptr, *tile_value = nullptr, *tile_majorant = nullptr, *bricks = nullptr, *slot_majorant = nullptr;
     size_t bytes = 0;
     void release()
     {
-        cudaFree(cells); cudaFree(slots); cudaFree(tile_value); cudaFree(tile_majorant); cudaFree(bricks);
-        cells = slots = tile_value = tile_majorant = bricks = nullptr; bytes = 0;
+        cudaFree(cells); cudaFree(slots); cudaFree(tile_value); cudaFree(tile_majorant); cudaFree(bricks); cudaFree(slot_majorant);
+        cells = slots = tile_value = tile_majorant = bricks = slot_majorant = nullptr; bytes = 0;
     }
 };
 
@@ -101,7 +101,9 @@ int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
     if ((e = up(&g.cells, b.cells.data(), b.cells.size() * 4)) != cudaSuccess || (e = up(&g.slots, b.slots.data(), b.slots.size() * 4)) != cudaSuccess ||
         (e = up(&g.tile_value, b.tile_value.data(), b.tile_value.size() * 4)) != cudaSuccess ||
         (e = up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4)) != cudaSuccess ||
-        (e = up(&g.bricks, b.bricks.data(), b.bricks.size() * 4)) != cudaSuccess || (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) {
+        (e = up(&g.bricks, b.bricks.data(), b.bricks.size() * 4)) != cudaSuccess ||
+        (!b.slot_majorant.empty() && (e = up(&g.slot_majorant, b.slot_majorant.data(), b.slot_majorant.size() * 4)) != cudaSuccess) ||
+        (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) {
         cudaStreamSynchronize(ctx->stream); // the host vectors must outlive any copy still in flight
         g.release();
         cudaGetLastError();
@@ -112,6 +114,7 @@ int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
     g.dev.tile_value = static_cast<const float*>(g.tile_value);
     g.dev.tile_majorant = static_cast<const float*>(g.tile_majorant);
     g.dev.bricks = static_cast<const float*>(g.bricks);
+    g.dev.slot_majorant = static_cast<const float*>(g.slot_majorant);
     return VPTC_OK;
 }
 
