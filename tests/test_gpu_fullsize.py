@@ -59,3 +59,52 @@ def test_fullsize_properties(renderer, oracle, api, scenes, name, factor):
     print(f"\n[{name} x{factor}] {W}x{H}: 48 sampled jobs bit-equal to the oracle; per pixel-sample: "
           f"{c12['density_evals'] / c12['pixel_samples']:.1f} density evals, {c12['majorant_fetches'] / c12['pixel_samples']:.1f} majorant fetches, "
           f"{c12['rng_draws'] / c12['pixel_samples']:.1f} draws")
+
+
+# (config, GPU waves with the second-moment plane, independent CPU waves): the CPU renders the full frame, so its share is kept to ~20 s
+STATS_CASES = [("wdas_cloud", 64, 8), ("fire", 64, 16), ("fire_lowscattering", 64, 16)]
+
+
+@pytest.mark.parametrize("name,gpu_waves,cpu_waves", STATS_CASES)
+def test_fullsize_image_statistics(renderer, oracle, api, scenes, name, gpu_waves, cpu_waves):
+    """BASELINE configs 1-3 at FULL resolution: the GPU image against INDEPENDENT waves of the CPU oracle, per pixel inside 3 sigma, relMSE
+    stated. sigma comes from the GPU's own second-moment plane (vptc_render_adaptive with rel_error = 0 is the plain render + sum of y^2):
+    var(y_gpu_mean - y_cpu_mean) = s^2 (1/Ng + 1/Nc). Radiance is heavy-tailed, so the score sits below the Gaussian 0.9973; the CONTROL is a
+    second GPU render of yet other waves scored the same way (per wave the GPU film IS the CPU film, so it is the same estimator)."""
+    import json
+    scene, spec = scenes.load_config(name)
+    if name.startswith("wdas") and _CLOUD_FACTOR != 1.0:
+        spec = spec.scaled(_CLOUD_FACTOR)
+    key = (spec.kind, tuple(spec.dims), spec.voxel_size, spec.seed, tuple(spec.anchor))
+    if key not in _volumes:
+        _volumes.clear()
+        _volumes[key] = api.synth_volume(spec.kind, spec.dims, spec.voxel_size, spec.seed, spec.anchor)
+        renderer.set_volume(_volumes[key])
+    grids = _volumes[key]
+    H, W = scene.height, scene.width
+    film, sq, tw = renderer.run_adaptive(scene, np.zeros((H, W, 4), np.float32), gpu_waves, gpu_waves, 0.0, first_wave=1000)
+    assert (film[..., 3] == gpu_waves).all() and (tw == gpu_waves).all()
+    ctrl = renderer.run(scene, np.zeros((H, W, 4), np.float32), first_wave=5000, n_waves=cpu_waves)
+    cpu = np.zeros((H, W, 4), np.float32)
+    oracle.volume(grids).render(scene, cpu, first_wave=1, n_waves=cpu_waves)
+    assert (cpu[..., 3] == cpu_waves).all()
+    yg = film[..., 1].astype(np.float64) / gpu_waves
+    s2 = np.maximum(sq.astype(np.float64) - gpu_waves * yg * yg, 0.0) / (gpu_waves - 1)
+    sigma = np.sqrt(s2 * (1.0 / gpu_waves + 1.0 / cpu_waves))
+    floor = 1e-3 * max(yg.mean(), 1e-12)
+
+    def score(other):
+        yo = other[..., 1].astype(np.float64) / cpu_waves
+        z = np.abs(yo - yg) / np.maximum(sigma, floor)
+        return float((z <= 3).mean()), float(np.mean((yo - yg) ** 2 / (yg ** 2 + 1e-4 * yg.mean() ** 2))), float(yo.mean())
+    (f_cpu, r_cpu, m_cpu), (f_ctl, r_ctl, m_ctl) = score(cpu), score(ctrl)
+    line = {"config": name, "frame": [W, H], "gpu_waves": gpu_waves, "independent_cpu_waves": cpu_waves, "within_3_sigma_cpu": round(f_cpu, 4),
+            "within_3_sigma_control": round(f_ctl, 4), "relMSE_cpu": r_cpu, "relMSE_control": r_ctl, "mean_y_gpu": float(yg.mean()), "mean_y_cpu": m_cpu,
+            "mean_y_control": m_ctl}
+    print("\n[fullres]", json.dumps(line))
+    if os.path.isdir("gpurun_out"):
+        with open("gpurun_out/fullres_stats.jsonl", "a") as f:
+            f.write(json.dumps(line) + "\n")
+    assert f_cpu >= 0.95 and abs(f_cpu - f_ctl) <= 0.005
+    assert abs(r_cpu - r_ctl) <= 0.05 * max(r_ctl, 1e-6) + 1e-6
+    assert abs(m_cpu - yg.mean()) <= 0.02 * yg.mean()
