@@ -317,6 +317,12 @@ def strong_scaling(args, r, rank, world, local, barrier):
             return coll_ms
 
         r.run_device(scene, film.data_ptr(), 1, 2, 1)  # warm-up of this frame size
+        if world > 1:  # ... and of the combine: NCCL sets up its point-to-point connections at the first gather (1.6 s at N = 8), like the W warm-up steps of the main loop
+            if mode == "waves":
+                reduce_film(film)
+            else:
+                gather_film_stripes(film, scene, rank, world)
+            torch.cuda.synchronize()
         # the whole job on rank 0 alone
         barrier()
         t1 = None

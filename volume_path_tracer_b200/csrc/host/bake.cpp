@@ -6,7 +6,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -120,6 +122,15 @@ void parallel_for(size_t n, F&& f)
 
 void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& out)
 {
+    const bool timing = std::getenv("VPT_BAKE_TIMING") != nullptr; // development aid: stage times on stderr
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto t_last = now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto t = now();
+        std::fprintf(stderr, "[bake] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count());
+        t_last = t;
+    };
     if (const char* bad = check_grid(data, bytes)) throw std::runtime_error(bad);
     const TreeView tv(data);
     validate_tree(tv, bytes);
@@ -242,6 +253,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         for (size_t r = 0; r < nLeaf; ++r) brick_of[keyed[r].second] = uint32_t(r);
     }
 
+    lap("validate + tiles + cells");
     // ---- lower slots (codes now, majorants after the patch) ----
     out.slots.assign(nLower * 4096 * 2, 0u);
     for (size_t li = 0; li < nLower; ++li) {
@@ -262,6 +274,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         }
     }
 
+    lap("lower slots");
     // ---- bricks with +1 apron, and patched maxima ----
     out.bricks.assign(nLeaf * size_t(BRICK_STRIDE), 0.0f);
     out.brick_max.assign(nLeaf, 0.0f);
@@ -299,6 +312,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         }
         out.brick_max[bi] = m;
     });
+    lap("bricks + halo patch");
     std::vector<float> max_by_brick(nLeaf);
     for (size_t i = 0; i < nLeaf; ++i) max_by_brick[brick_of[i]] = out.brick_max[i];
     for (size_t e = 0; e < nLower * 4096; ++e) {
@@ -311,6 +325,7 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
         for (uint32_t n = 0; n < 4096; ++n)
             std::memcpy(&out.slot_majorant[li * 4096 + maj_index(n >> 8, (n >> 4) & 15u, n & 15u)], &out.slots[(li * 4096 + n) * 2 + 1], 4);
 #endif
+    lap("majorants into slots");
     h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
     h.background_tile = 0;
 }
