@@ -23,6 +23,12 @@
 
 namespace nvdbf {
 
+/* the bit helpers below are also used by the device-side baker (csrc/device/vpt_bake.cu) */
+#if defined(__CUDACC__)
+#define NVDBF_HD __host__ __device__
+#else
+#define NVDBF_HD
+#endif
 constexpr uint64_t MAGIC_NUMB = 0x304244566f6e614eULL; /* "NanoVDB0" */
 constexpr uint64_t MAGIC_GRID = 0x314244566f6e614eULL; /* "NanoVDB1" */
 constexpr uint64_t MAGIC_FILE = 0x324244566f6e614eULL; /* "NanoVDB2" */
@@ -92,11 +98,11 @@ struct RootTile { /* 32 B */
 };
 static_assert(sizeof(RootTile) == 32, "RootTile");
 
-inline uint64_t root_key(int32_t x, int32_t y, int32_t z)
+NVDBF_HD inline uint64_t root_key(int32_t x, int32_t y, int32_t z)
 {
     return (uint64_t(uint32_t(z)) >> 12) | ((uint64_t(uint32_t(y)) >> 12) << 21) | ((uint64_t(uint32_t(x)) >> 12) << 42);
 }
-inline void root_key_origin(uint64_t key, int32_t o[3])
+NVDBF_HD inline void root_key_origin(uint64_t key, int32_t o[3])
 {
     const uint64_t M = (1u << 21) - 1;
     o[0] = int32_t(uint32_t(((key >> 42) & M) << 12));
@@ -132,20 +138,20 @@ struct LeafData { /* 2144 B */
 static_assert(sizeof(LeafData) == 2144 && offsetof(LeafData, values) == 96 &&
               offsetof(LeafData, maximum) == 84, "Leaf");
 
-inline uint32_t upper_offset(int32_t x, int32_t y, int32_t z)
+NVDBF_HD inline uint32_t upper_offset(int32_t x, int32_t y, int32_t z)
 {
     return (uint32_t((x & 4095) >> 7) << 10) | (uint32_t((y & 4095) >> 7) << 5) | uint32_t((z & 4095) >> 7);
 }
-inline uint32_t lower_offset(int32_t x, int32_t y, int32_t z)
+NVDBF_HD inline uint32_t lower_offset(int32_t x, int32_t y, int32_t z)
 {
     return (uint32_t((x & 127) >> 3) << 8) | (uint32_t((y & 127) >> 3) << 4) | uint32_t((z & 127) >> 3);
 }
-inline uint32_t leaf_offset(int32_t x, int32_t y, int32_t z)
+NVDBF_HD inline uint32_t leaf_offset(int32_t x, int32_t y, int32_t z)
 {
     return (uint32_t(x & 7) << 6) | (uint32_t(y & 7) << 3) | uint32_t(z & 7);
 }
-inline bool mask_on(const uint64_t* words, uint32_t n) { return (words[n >> 6] >> (n & 63)) & 1u; }
-inline void mask_set(uint64_t* words, uint32_t n) { words[n >> 6] |= uint64_t(1) << (n & 63); }
+NVDBF_HD inline bool mask_on(const uint64_t* words, uint32_t n) { return (words[n >> 6] >> (n & 63)) & 1u; }
+NVDBF_HD inline void mask_set(uint64_t* words, uint32_t n) { words[n >> 6] |= uint64_t(1) << (n & 63); }
 
 /* ---- .nvdb file segments (uncompressed or ZIP codec) ---- */
 struct FileHeader { uint64_t magic; uint32_t version; uint16_t gridCount; uint16_t codec; };
@@ -164,13 +170,13 @@ struct FileMetaData { /* 176 B, followed by nameSize chars (incl. NUL) */
 };
 static_assert(sizeof(FileMetaData) == 176, "FileMetaData");
 
-inline const TreeData* tree_of(const GridData* g) { return reinterpret_cast<const TreeData*>(g + 1); }
-inline const RootData* root_of(const GridData* g)
+NVDBF_HD inline const TreeData* tree_of(const GridData* g) { return reinterpret_cast<const TreeData*>(g + 1); }
+NVDBF_HD inline const RootData* root_of(const GridData* g)
 {
     const TreeData* t = tree_of(g);
     return reinterpret_cast<const RootData*>(reinterpret_cast<const char*>(t) + t->nodeOffset[3]);
 }
-inline const RootTile* root_tiles(const RootData* r) { return reinterpret_cast<const RootTile*>(r + 1); }
+NVDBF_HD inline const RootTile* root_tiles(const RootData* r) { return reinterpret_cast<const RootTile*>(r + 1); }
 
 } // namespace nvdbf
 #endif

@@ -98,7 +98,9 @@ VPTC_API const char* vptc_last_error(const vptc_ctx* ctx);
  * takes the raw serialized NanoVDB grid buffers that nanovdb::io::readGrid returns (density
  * required, temperature optional: pass NULL/0), applies fix_majorants_for_interpolation
  * (volume.cpp:104-160) to a private copy — the caller's memory is never mutated and may be freed on
- * return — bakes the brick-sparse layout and stages it to HBM once. */
+ * return — bakes the brick-sparse layout and stages it to HBM once.  The tree is validated and its small tables are built on the host; the
+ * apron bricks and the halo patch are computed on the device from the uploaded grid (csrc/device/vpt_bake.cu; VPT_HOST_BAKE=1 in the
+ * environment keeps everything on the host threads, byte-identical result). */
 VPTC_API int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t density_bytes,
                              const void* temperature_grid, size_t temperature_bytes);
 

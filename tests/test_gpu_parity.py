@@ -646,3 +646,33 @@ def test_adaptive_image_within_monte_carlo_noise(renderer, oracle, loaded):
     got, control = inside(f, sq), inside(plain, sq_p)
     print(f"\n[adaptive vs CPU oracle, fire 70x100] inside 3 sigma: adaptive {got:.4f}, plain 256-wave control {control:.4f}; mean waves/tile {tw.mean():.1f} of 256")
     assert got > 0.985 and got > control - 0.01
+
+
+@pytest.mark.parametrize("name", ["fire", "wdas_cloud", "dense512"])
+def test_device_bake_equals_host_bake(api, small_case, monkeypatch, name):
+    """The brick stage of the baker on the device (csrc/device/vpt_bake.cu: apron bricks + fix_majorants_for_interpolation, volume.cpp:104-160)
+    against the host baker (csrc/host/bake.cpp, VPT_HOST_BAKE=1): same bytes on the device, probed through every lookup the kernels make —
+    values, getDim and patched majorants at points around every kind of boundary, trilinear samples through a rendered film."""
+    scene, spec, grids = small_case(name)
+    monkeypatch.delenv("VPT_HOST_BAKE", raising=False)
+    dev = api.Renderer(0); dev.set_volume(grids)
+    monkeypatch.setenv("VPT_HOST_BAKE", "1")
+    host = api.Renderer(0); host.set_volume(grids)
+    monkeypatch.delenv("VPT_HOST_BAKE", raising=False)
+    try:
+        assert dev.device_volume_bytes() == host.device_volume_bytes()
+        rs = np.random.default_rng(3)
+        d = np.asarray(spec.dims, np.float64)
+        pts = np.concatenate([
+            rs.random((20000, 3)) * (d + 24) - 12,                                   # anywhere, incl. outside the grid
+            np.round(rs.random((20000, 3)) * (d / 8)) * 8 + rs.integers(-1, 2, (20000, 3)),  # on and next to leaf faces (where the apron and the halo patch matter)
+        ]).astype(np.float32)
+        for grid_id in ((0, 1) if grids.temperature is not None else (0,)):
+            a, b = dev.sample_grid(grid_id, pts), host.sample_grid(grid_id, pts)
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y, equal_nan=True)
+        fa = dev.run(scene, dev.new_film(scene), 1, 1)
+        fb = host.run(scene, host.new_film(scene), 1, 1)
+        assert np.array_equal(fa, fb) and fa[..., :3].any()  # one wave: one sample per pixel, no add-order slack
+    finally:
+        dev.close(); host.close()

@@ -53,6 +53,9 @@ struct FilmSources { const float4* p[FILM_REDUCE_MAX_SRC]; };
 // dst (n_pixels float4 on the current device) += sum of k <= FILM_REDUCE_MAX_SRC source films, which may be peer-mapped memory of other devices
 cudaError_t launch_film_reduce(float* dst, const float* const* srcs, int k, size_t n_pixels, cudaStream_t s);
 cudaError_t launch_blackbody(const float* bb_table, const float* temps, size_t n, float* xyz, cudaStream_t s);
+// device-side brick stage of the baker (device/vpt_bake.cu): apron bricks + patched leaf maxima from the serialized grid in device memory
+cudaError_t launch_bake_bricks(const void* d_grid, uint64_t n_leaf, const uint32_t* d_brick_of, bool patch, float* d_bricks, float* d_max_by_brick,
+                               void* d_slots, uint64_t n_slots, cudaStream_t s);
 cudaError_t launch_resolve(const float* film, size_t n_pixels, uint8_t* rgb, cudaStream_t s);
 
 } // namespace vptd

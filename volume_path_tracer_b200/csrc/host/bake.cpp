@@ -120,7 +120,7 @@ void parallel_for(size_t n, F&& f)
 
 } // namespace
 
-void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& out)
+void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& out, bool device_bricks)
 {
     const bool timing = std::getenv("VPT_BAKE_TIMING") != nullptr; // development aid: stage times on stderr
     auto now = [] { return std::chrono::steady_clock::now(); };
@@ -275,6 +275,14 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
     }
 
     lap("lower slots");
+    h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
+    h.background_tile = 0;
+    out.device_bricks = device_bricks; out.patch_majorants = patch_majorants;
+    out.raw = data; out.raw_bytes = size_t(std::min<uint64_t>(g->gridSize, bytes));
+    bool identity = true;
+    for (size_t i = 0; i < nLeaf && identity; ++i) identity = brick_of[i] == uint32_t(i);
+    if (!identity) out.brick_of = brick_of; else out.brick_of.clear();
+    if (device_bricks) { out.bricks.clear(); out.brick_max.clear(); return; } // the brick stage runs on the device (device/vpt_bake.cu)
     // ---- bricks with +1 apron, and patched maxima ----
     out.bricks.assign(nLeaf * size_t(BRICK_STRIDE), 0.0f);
     out.brick_max.assign(nLeaf, 0.0f);
@@ -326,8 +334,6 @@ void bake_grid(const void* data, size_t bytes, bool patch_majorants, BakedGrid& 
             std::memcpy(&out.slot_majorant[li * 4096 + maj_index(n >> 8, (n >> 4) & 15u, n & 15u)], &out.slots[(li * 4096 + n) * 2 + 1], 4);
 #endif
     lap("majorants into slots");
-    h.n_lower = uint32_t(nLower); h.n_bricks = uint32_t(nLeaf); h.n_tiles = uint32_t(out.tile_value.size());
-    h.background_tile = 0;
 }
 
 } // namespace vpt_host

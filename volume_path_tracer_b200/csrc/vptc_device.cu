@@ -97,11 +97,31 @@ int upload(vptc_ctx* ctx, const vpt_host::BakedGrid& b, DeviceGrid& g)
         g.bytes += bytes;
         return bytes ? cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
     };
+    // The brick stage on the device (device/vpt_bake.cu): the caller's serialized grid is staged as it is, one block per leaf fills its apron
+    // brick and reduces the patched maximum, a second pass folds the maxima into the slot table uploaded just before. Temporaries are freed here.
+    void *d_raw = nullptr, *d_max = nullptr, *d_order = nullptr;
+    auto device_brick_stage = [&]() -> cudaError_t {
+        const size_t nb = b.header.n_bricks, brick_bytes = nb * size_t(BRICK_STRIDE) * 4;
+        cudaError_t e = cudaMalloc(&g.bricks, brick_bytes ? brick_bytes : 16);
+        if (e != cudaSuccess) return e;
+        g.bytes += brick_bytes;
+        if (nb == 0) return cudaSuccess;
+        if ((e = cudaMemsetAsync(g.bricks, 0, brick_bytes, ctx->stream)) != cudaSuccess) return e; // the padding floats of a brick are zero, as in the host baker
+        if ((e = cudaMalloc(&d_raw, b.raw_bytes)) != cudaSuccess || (e = cudaMalloc(&d_max, nb * 4)) != cudaSuccess) return e;
+        if ((e = cudaMemcpyAsync(d_raw, b.raw, b.raw_bytes, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return e;
+        if (!b.brick_of.empty()) {
+            if ((e = cudaMalloc(&d_order, nb * 4)) != cudaSuccess) return e;
+            if ((e = cudaMemcpyAsync(d_order, b.brick_of.data(), nb * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return e;
+        }
+        return launch_bake_bricks(d_raw, nb, static_cast<const uint32_t*>(d_order), b.patch_majorants, static_cast<float*>(g.bricks), static_cast<float*>(d_max),
+                                  g.slots, b.slots.size() / 2, ctx->stream);
+    };
+    struct Temps { void *&a, *&b, *&c; ~Temps() { cudaFree(a); cudaFree(b); cudaFree(c); } } temps{d_raw, d_max, d_order}; // after the stream synchronisation below
     cudaError_t e;
     if ((e = up(&g.cells, b.cells.data(), b.cells.size() * 4)) != cudaSuccess || (e = up(&g.slots, b.slots.data(), b.slots.size() * 4)) != cudaSuccess ||
         (e = up(&g.tile_value, b.tile_value.data(), b.tile_value.size() * 4)) != cudaSuccess ||
         (e = up(&g.tile_majorant, b.tile_majorant.data(), b.tile_majorant.size() * 4)) != cudaSuccess ||
-        (e = up(&g.bricks, b.bricks.data(), b.bricks.size() * 4)) != cudaSuccess ||
+        (e = b.device_bricks ? device_brick_stage() : up(&g.bricks, b.bricks.data(), b.bricks.size() * 4)) != cudaSuccess ||
         (!b.slot_majorant.empty() && (e = up(&g.slot_majorant, b.slot_majorant.data(), b.slot_majorant.size() * 4)) != cudaSuccess) ||
         (e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) {
         cudaStreamSynchronize(ctx->stream); // the host vectors must outlive any copy still in flight
@@ -336,9 +356,11 @@ int bake_volume(vptc_ctx* ctx, const void* density_grid, size_t density_bytes, c
 {
     has_temperature = false;
     try {
-        vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b);
+        // the brick stage (97 % of the bake) runs on the device unless asked otherwise; the split-majorant experiment builds its table on the host
+        const bool device_bricks = !std::getenv("VPT_HOST_BAKE") && !VPT_SPLIT_MAJ;
+        vpt_host::bake_grid(density_grid, density_bytes, /*patch_majorants=*/true, b, device_bricks);
         if (temperature_grid && temperature_bytes) {
-            vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t);
+            vpt_host::bake_grid(temperature_grid, temperature_bytes, /*patch_majorants=*/false, t, device_bricks);
             has_temperature = true;
         }
     } catch (const std::exception& e) {
