@@ -3,8 +3,9 @@
 // Minimal stand-in for the Eigen::Vector3f / Affine3f operations the reference's hot path uses. Eigen
 // is not installed in this image, so its association order is adopted from
 // Eigen's fixed-size scalar reduction (redux_novec_unroller, halves): for 3 terms x0 + (x1 + x2);
-// normalized() = v / sqrt(squaredNorm) with a true division per component. "Parity unpinned" for
-// these few operations (effect <= 1 ulp on directions); the GPU code copies THIS order.
+// normalized() = v / sqrt(squaredNorm) with a true division per component. This order is the one choice that
+// cannot be verified here (effect <= 1 ulp on directions): the compiled reference (oracle/ref/eigen_shim) and the
+// GPU code use THIS order too, so everything else is pinned around it.
 #pragma once
 #include <cmath>
 

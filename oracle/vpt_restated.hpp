@@ -10,8 +10,11 @@
 //
 // Pinning: the reference has no tests or golden outputs; this restatement is pinned by
 // running it on the reference's own vendored arithmetic (oracle/_ref) and comparing with the
-// self-contained build bit for bit (tests/test_oracle_ref.py), plus NanoVDB unit-test known answers.
-// The handful of Eigen reductions are "parity unpinned" (Eigen absent; see vec3.hpp).
+// self-contained build bit for bit (tests/test_oracle_ref.py), plus NanoVDB unit-test known answers — and, since round 2, by THE
+// REFERENCE'S OWN src/*.cpp compiled unchanged into oracle/_ref/libvpt_reference.so (oracle/Makefile `ref`, oracle/ref/reference_capi.cpp):
+// tests/test_reference_compiled.py asserts this restatement equals that library bit for bit (films of vpt::run, segments, collisions,
+// patched maxima, camera, tiles, RNG, blackbody, HG, film_to_image, dda_trace.csv). Parity is pinned; the one thing no build on this
+// machine can check is Eigen's own association order in 3-term reductions (Eigen is absent: the stand-in header and vec3.hpp use a + (b + c)).
 #pragma once
 #include <algorithm>
 #include <array>
