@@ -43,6 +43,13 @@ namespace vptd {
 #ifndef VPT_DEFER_INF
 #define VPT_DEFER_INF 0 // a ray that leaves the volume only marks the pixel; the infinite light is added where the pixel is closed (no cold-state traffic in HOT)
 #endif
+#ifndef VPT_FILM_IN_COLD
+#define VPT_FILM_IN_COLD 0 // the film pointer of the lane's current range is kept in two cold words (written at the job fetch) instead of being re-read from the
+                           // ring descriptor (an L2 round trip) at every pixel: matters where a pixel-sample is cheap (fire: ~10 HDDA steps)
+#endif
+#ifndef VPT_FETCH_DIV32
+#define VPT_FETCH_DIV32 1 // job fetch: 32-bit divisions where the operands fit, tile taken from the decomposition instead of jid % ntiles (profiles/r02_kernel_ab.txt)
+#endif
 #ifndef VPT_LOOKAHEAD
 #define VPT_LOOKAHEAD 0 // the HDDA runs ONE STEP AHEAD of the segment logic: a pass first takes the pair (t0, majorant) whose load the previous pass issued, steps again and
                         // issues the next load, and only then consumes the pair — a whole pass between a slot load and its use (profiles/r02_kernel_ab.txt)
@@ -102,7 +109,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     // touches — path origin/direction/radiance, shadow transmittance, depth, the job's pixel bookkeeping, the
     // temperature grid's cell cache. That is 21 registers the hot loop does not have to carry, which is what lets
     // the kernel fit VPT_SCHED_MIN_BLOCKS resident blocks per SM without spilling.
-    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_RANGE = 21, C_WORDS = 22 };
+    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_RANGE = 21, C_FILM = 22, C_WORDS = 22 + 2 * VPT_FILM_IN_COLD };
     __shared__ uint32_t cold[C_WORDS][VPT_BLOCK_THREADS];
     const int lane_col = threadIdx.x;
 #define CLDF(i) __uint_as_float(cold[i][lane_col])
@@ -173,7 +180,11 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         A.trace_xyz[slot * 3 + 0] = L.x; A.trace_xyz[slot * 3 + 1] = L.y; A.trace_xyz[slot * 3 + 2] = L.z;
                         A.trace_ndraws[slot] = rng.draws;
                     } else {
+#if VPT_FILM_IN_COLD
+                        float* film = reinterpret_cast<float*>((unsigned long long)(cold[C_FILM][lane_col]) | ((unsigned long long)(cold[C_FILM + 1][lane_col]) << 32));
+#else
                         float* film = reinterpret_cast<float*>(__ldcg(reinterpret_cast<const unsigned long long*>(&A.ring[cold[C_RANGE][lane_col] % RING_SLOTS].film))); // the film of the call this job belongs to
+#endif
                         film_add(film + (size_t(y0 + y) * size_t(S.W) + size_t(x0 + x)) * 4, S.imaging_ratio * L.x, S.imaging_ratio * L.y, S.imaging_ratio * L.z);
                         if (STATS) {
                             float* sq = reinterpret_cast<float*>(__ldcg(reinterpret_cast<const unsigned long long*>(&A.ring[cold[C_RANGE][lane_col] % RING_SLOTS].sum_y2)));
@@ -210,22 +221,48 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                             R = A.ring + (rc % RING_SLOTS);
                         }
                         cold[C_RANGE][lane_col] = rc;
+#if VPT_FILM_IN_COLD
+                        if (!TRACE && stage != ST_EXIT) {
+                            const unsigned long long fp = __ldcg(reinterpret_cast<const unsigned long long*>(&R->film));
+                            cold[C_FILM][lane_col] = uint32_t(fp); cold[C_FILM + 1][lane_col] = uint32_t(fp >> 32);
+                        }
+#endif
                         if (stage == ST_EXIT) { CSTI(C_SY, 0); atomicAdd(A.exited, 1u); break; }
-                        uint64_t jid;
-                        if (TRACE) jid = A.trace_jids[j];
+                        uint64_t jid, tile;
+                        if (TRACE) { jid = A.trace_jids[j]; tile = jid % S.ntiles; }
                         else {
                             const uint64_t tcount = __ldcg(&R->tile_count);
+#if VPT_FETCH_DIV32
+                            // the 64-bit divisions are library calls of ~70 instructions each, run by ONE lane while 31 wait: where every operand fits
+                            // 32 bits (any frame below 2^32 jobs per call) the inline 32-bit form does the same arithmetic
+                            uint64_t k, ti, trow;
+                            if (((j | tcount) >> 32) == 0) {
+                                const uint32_t k32 = uint32_t(j) / uint32_t(tcount);
+                                k = k32; ti = uint32_t(j) - k32 * uint32_t(tcount); trow = uint32_t(ti) / uint32_t(S.ntx);
+                            } else { k = j / tcount; ti = j - k * tcount; trow = ti / uint64_t(S.ntx); }
+#else
                             const uint64_t k = j / tcount;
                             const uint64_t ti = j - k * tcount, trow = ti / uint64_t(S.ntx); // interleaved stripes: every tile_row_stride-th row of tiles
+#endif
                             uint64_t tile_k = __ldcg(&R->tile_begin) + trow * (uint64_t(__ldcg(&R->tile_row_stride)) * uint64_t(S.ntx)) + (ti - trow * uint64_t(S.ntx));
                             if (STATS) {
                                 const uint32_t* list = reinterpret_cast<const uint32_t*>(__ldcg(reinterpret_cast<const unsigned long long*>(&R->tile_list)));
-                                if (list) tile_k = __ldg(list + (j - k * tcount));
+                                if (list) tile_k = __ldg(list + ti);
                             }
                             jid = (uint64_t(__ldcg(&R->first_wave) - 1u) + k * __ldcg(&R->wave_stride)) * S.ntiles + tile_k;
+#if VPT_FETCH_DIV32
+                            tile = tile_k; // = jid % ntiles by construction (tile_k < ntiles)
+#else
+                            tile = jid % S.ntiles;
+#endif
                         }
-                        const uint64_t tile = jid % S.ntiles;
+#if VPT_FETCH_DIV32
+                        uint64_t tyq;
+                        if ((tile >> 32) == 0) tyq = uint32_t(tile) / uint32_t(S.ntx); else tyq = tile / uint64_t(S.ntx);
+                        const int64_t tx0 = int64_t(tile - tyq * uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tyq) * S.th;
+#else
                         const int64_t tx0 = int64_t(tile % uint64_t(S.ntx)) * S.tw, ty0 = int64_t(tile / uint64_t(S.ntx)) * S.th;
+#endif
                         x0 = int(tx0); y0 = int(ty0);
                         sx = int(min(S.W - tx0, S.tw)); sy = int(min(S.H - ty0, S.th));
                         CSTI(C_X0, x0); CSTI(C_Y0, y0); CSTI(C_SX, sx); CSTI(C_SY, sy);
