@@ -676,3 +676,39 @@ def test_device_bake_equals_host_bake(api, small_case, monkeypatch, name):
         assert np.array_equal(fa, fb) and fa[..., :3].any()  # one wave: one sample per pixel, no add-order slack
     finally:
         dev.close(); host.close()
+
+
+def test_tile_order_keeps_every_sample(api, small_case, monkeypatch):
+    """Longest-tiles-first (DESIGN.md "launch drain"): once a scene's per-tile job times are known, full-frame ranges are walked tile-major in
+    cost order by the ORD = 2 instantiation. Job ids are unchanged, so: one wave rendered ordered is BIT-equal to the same wave rendered in
+    natural order (one sample per pixel: no add-order slack), multi-wave films agree to add order with exact counts, and a series that mixes
+    ordered full-frame calls with tile-stripe calls (plain launches) still renders every job exactly once."""
+    import torch
+    scene, spec, grids = small_case("dense512")
+    monkeypatch.setenv("VPT_TILE_ORDER", "0")
+    plain = api.Renderer(0); plain.set_volume(grids)
+    monkeypatch.delenv("VPT_TILE_ORDER")
+    r = api.Renderer(0); r.set_volume(grids)
+    try:
+        H, W = scene.height, scene.width
+        r.run(scene, r.new_film(scene), 1, 2)          # learning calls: natural order, per-tile times recorded
+        a = r.run(scene, r.new_film(scene), 7, 1)      # ordered from here on
+        b = plain.run(scene, plain.new_film(scene), 7, 1)
+        assert np.array_equal(a, b) and (a[..., 3] == 1).all()
+        a = r.run(scene, r.new_film(scene), 3, 6)
+        b = plain.run(scene, plain.new_film(scene), 3, 6)
+        assert np.array_equal(a[..., 3], b[..., 3]) and (a[..., 3] == 6).all() and np.allclose(a, b, rtol=1e-5, atol=1e-7)
+        # asynchronous series on a device film: ordered full frames, then a stripe of tiles (a plain launch), then full frames again
+        d = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda:0")
+        ntx = -(-W // int(scene.tile_size[0])); nty = -(-H // int(scene.tile_size[1]))
+        r.run_device_range(scene, d.data_ptr(), 1, 2, wait=False)
+        r.run_device_range(scene, d.data_ptr(), 3, 1, tile_begin=0, tile_count=ntx * (nty // 2), wait=False)
+        r.run_device_range(scene, d.data_ptr(), 3, 1, tile_begin=ntx * (nty // 2), tile_count=ntx * (nty - nty // 2), wait=False)
+        r.run_device_range(scene, d.data_ptr(), 4, 3, wait=False)
+        r.wait()
+        torch.cuda.synchronize()
+        got = d.cpu().numpy()
+        want = plain.run(scene, plain.new_film(scene), 1, 6)
+        assert np.array_equal(got[..., 3], want[..., 3]) and (got[..., 3] == 6).all() and np.allclose(got, want, rtol=1e-5, atol=1e-7)
+    finally:
+        r.close(); plain.close()

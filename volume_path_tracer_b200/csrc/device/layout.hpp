@@ -113,11 +113,11 @@ struct SceneDev {
 // takes jobs from its own call's range and, when that is exhausted, carries on into the next published one instead of draining — so a
 // progressive render made of many small calls keeps every lane busy across call boundaries (DESIGN.md "launch drain"). A range may also
 // cover only a stripe of tiles [tile_begin, tile_begin + tile_count) (multi-GPU tile sharding, src/tile_provider.cpp:95-105).
-//   job j of the range:  k = j / tile_count,  i = j % tile_count,  tile = tile_begin + (i / ntx) * tile_row_stride * ntx + i % ntx,
+//   job j of the range (no tile_list):  k = j / tile_count,  i = j % tile_count,  tile = tile_begin + (i / ntx) * tile_row_stride * ntx + i % ntx,
 //                        jid = (first_wave - 1 + k * wave_stride) * ntiles + tile
 //   (tile_row_stride 1: the contiguous stripe; G: every G-th ROW of tiles starting at row tile_begin / ntx — interleaved stripes balance the load)
 constexpr unsigned RING_SLOTS = 64;
-struct RangeDesc { // 80 bytes
+struct RangeDesc { // 96 bytes
     unsigned long long counter;  // next job index of the range = TileProvider::m_job_idx (tile_provider.cpp:28); device atomics only
     unsigned long long done;     // jobs finished; the lane that makes it n_jobs raises host_done[slot]
     unsigned long long n_jobs;   // tile_count * n_waves
@@ -128,8 +128,12 @@ struct RangeDesc { // 80 bytes
     // statistics launches only (the STATS instantiation of the kernel; adaptive rendering):
     const uint32_t* tile_list;   // when set: the range covers tile_list[0 .. tile_count) instead of a contiguous stripe
     float* sum_y2;               // when set: H*W floats, += (imaging_ratio * L.y)^2 per pixel-sample (second moment of the luminance)
+    // tile order (longest jobs first, DESIGN.md "launch drain"): with a tile_list the range is walked TILE-MAJOR — job j is wave j % n_waves of
+    // tile_list[j / n_waves] — so that every wave of the expensive tiles starts at once and the cheap tiles fill the tail;
+    uint32_t* tile_cost;         // when set: [ntiles] += SM clock ticks >> 10 a job of the tile took (how the order is learnt)
+    uint32_t n_waves, pad_;      // n_jobs / tile_count
 };
-static_assert(sizeof(RangeDesc) == 80, "RangeDesc");
+static_assert(sizeof(RangeDesc) == 96, "RangeDesc");
 
 struct CountersDev {
     unsigned long long pixel_samples, density_evals, temperature_evals, majorant_fetches, rng_draws, scatter_events, shadow_rays;

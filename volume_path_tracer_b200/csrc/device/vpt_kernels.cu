@@ -310,6 +310,19 @@ cudaError_t launch_render_stats(const RenderArgs& args, int grid_blocks, cudaStr
     vpt_render_sched_kernel<false, false, true><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
     return cudaGetLastError();
 }
+cudaError_t launch_render_ordered(const RenderArgs& args, int ord, int grid_blocks, cudaStream_t stream) // tile order: 1 = learning, 2 = ordered
+{
+    if (ord == 1) vpt_render_sched_kernel<false, false, false, 1><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    else vpt_render_sched_kernel<false, false, false, 2><<<grid_blocks, VPT_BLOCK_THREADS, 0, stream>>>(args);
+    return cudaGetLastError();
+}
+int render_ordered_blocks_per_sm(int ord)
+{
+    int n = 0;
+    const cudaError_t e = ord == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<false, false, false, 1>, VPT_BLOCK_THREADS, 0)
+                                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vpt_render_sched_kernel<false, false, false, 2>, VPT_BLOCK_THREADS, 0);
+    return e == cudaSuccess ? n : 0;
+}
 int render_stats_blocks_per_sm()
 {
     int n = 0;

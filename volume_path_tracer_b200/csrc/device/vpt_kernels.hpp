@@ -44,6 +44,8 @@ cudaError_t launch_render(const RenderArgs& args, int variant, bool trace, bool 
 int render_blocks_per_sm(int variant, bool trace, bool count);
 cudaError_t launch_render_stats(const RenderArgs& args, int grid_blocks, cudaStream_t stream); // default kernel + tile lists + second-moment plane (adaptive rendering)
 int render_stats_blocks_per_sm();
+cudaError_t launch_render_ordered(const RenderArgs& args, int ord, int grid_blocks, cudaStream_t stream); // default kernel, tile-order instantiations: 1 learn, 2 ordered
+int render_ordered_blocks_per_sm(int ord);
 cudaError_t launch_tile_error(const float* film, const float* sum_y2, long long W, long long H, long long tw, long long th, long long ntx, unsigned long long ntiles, float* err, cudaStream_t s);
 int render_jobs_per_block(int variant); // jobs a resident block works on at a time (grid sizing)
 cudaError_t launch_segments(const GridDev& G, const float* origins, const float* dirs, size_t n, uint32_t max_segs, float* segs, uint32_t* n_segs, cudaStream_t s);

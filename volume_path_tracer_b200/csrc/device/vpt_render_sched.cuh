@@ -60,7 +60,9 @@ enum : int { PH_NEXT_PIXEL_INF = 5 }; // NEXT_PIXEL for a path that escaped to t
 // STATS: the instantiation adaptive rendering launches — an explicit tile list per range and a second-moment plane beside the film. A template
 // parameter, not a run-time test, so that the production instantiation's SASS does not change (the job fetch is where one extra conditional
 // load once cost 25 %: profiles/r01_codegen_cliff.txt).
-template <bool TRACE, bool COUNT, bool STATS = false>
+// ORD: the tile-order instantiations (launch_render_ordered) — 1 LEARNS (natural order, each finished job adds its duration to the range's
+// tile_cost), 2 walks the range's tile_list tile-major. Template parameters for the same reason as STATS: ORD = 0 is the kernel as it was.
+template <bool TRACE, bool COUNT, bool STATS = false, int ORD = 0>
 __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_render_sched_kernel(const RenderArgs A)
 {
     __shared__ float bb[1504];
@@ -109,7 +111,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
     // touches — path origin/direction/radiance, shadow transmittance, depth, the job's pixel bookkeeping, the
     // temperature grid's cell cache. That is 21 registers the hot loop does not have to carry, which is what lets
     // the kernel fit VPT_SCHED_MIN_BLOCKS resident blocks per SM without spilling.
-    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_RANGE = 21, C_FILM = 22, C_WORDS = 22 + 2 * VPT_FILM_IN_COLD };
+    enum { C_POS = 0, C_RD = 3, C_L = 6, C_TRAY = 9, C_DEPTH = 10, C_X0 = 11, C_Y0 = 12, C_SX = 13, C_SY = 14, C_X = 15, C_Y = 16, C_CT = 17, C_RANGE = 21, C_FILM = 22, C_TILE = 22 + 2 * VPT_FILM_IN_COLD, C_T0 = C_TILE + 1, C_WORDS = 22 + 2 * VPT_FILM_IN_COLD + 2 * (ORD == 1) };
     __shared__ uint32_t cold[C_WORDS][VPT_BLOCK_THREADS];
     const int lane_col = threadIdx.x;
 #define CLDF(i) __uint_as_float(cold[i][lane_col])
@@ -203,6 +205,10 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         unsigned int rc = cold[C_RANGE][lane_col];
                         RangeDesc* R = A.ring + (rc % RING_SLOTS);
                         if (sy > 0) { // a job of range rc just finished: count it; the last one raises the host's completion flag
+                            if (ORD == 1) { // how long the job took, per tile: what the host sorts the next calls' tiles by
+                                uint32_t* cost = reinterpret_cast<uint32_t*>(__ldcg(reinterpret_cast<const unsigned long long*>(&R->tile_cost)));
+                                if (cost) atomicAdd(cost + cold[C_TILE][lane_col], max(1u, (uint32_t(clock()) - cold[C_T0][lane_col]) >> 10));
+                            }
                             __threadfence(); // this lane's film reductions before the count
                             if (atomicAdd(&R->done, 1ULL) + 1ULL == __ldcg(&R->n_jobs)) {
                                 __threadfence_system();
@@ -241,13 +247,18 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                                 k = k32; ti = uint32_t(j) - k32 * uint32_t(tcount); trow = uint32_t(ti) / uint32_t(S.ntx);
                             } else { k = j / tcount; ti = j - k * tcount; trow = ti / uint64_t(S.ntx); }
 #else
-                            const uint64_t k = j / tcount;
+                            uint64_t k = j / tcount;
                             const uint64_t ti = j - k * tcount, trow = ti / uint64_t(S.ntx); // interleaved stripes: every tile_row_stride-th row of tiles
 #endif
                             uint64_t tile_k = __ldcg(&R->tile_begin) + trow * (uint64_t(__ldcg(&R->tile_row_stride)) * uint64_t(S.ntx)) + (ti - trow * uint64_t(S.ntx));
-                            if (STATS) {
+                            if (STATS || ORD == 2) { // explicit tile list: the range is walked tile-major (layout.hpp RangeDesc)
                                 const uint32_t* list = reinterpret_cast<const uint32_t*>(__ldcg(reinterpret_cast<const unsigned long long*>(&R->tile_list)));
-                                if (list) tile_k = __ldg(list + ti);
+                                if (list) {
+                                    const uint32_t nw = __ldcg(&R->n_waves);
+                                    const uint64_t slot = ((j >> 32) == 0) ? uint64_t(uint32_t(j) / nw) : j / nw;
+                                    k = j - slot * nw;
+                                    tile_k = __ldg(list + slot);
+                                }
                             }
                             jid = (uint64_t(__ldcg(&R->first_wave) - 1u) + k * __ldcg(&R->wave_stride)) * S.ntiles + tile_k;
 #if VPT_FETCH_DIV32
@@ -266,6 +277,7 @@ __global__ void __launch_bounds__(VPT_BLOCK_THREADS, VPT_SCHED_MIN_BLOCKS) vpt_r
                         x0 = int(tx0); y0 = int(ty0);
                         sx = int(min(S.W - tx0, S.tw)); sy = int(min(S.H - ty0, S.th));
                         CSTI(C_X0, x0); CSTI(C_Y0, y0); CSTI(C_SX, sx); CSTI(C_SY, sy);
+                        if (ORD == 1) { cold[C_TILE][lane_col] = uint32_t(tile); cold[C_T0][lane_col] = uint32_t(clock()); }
                         rng.begin_job(S.seed, jid);
                         x = 0; y = 0;
                     }

@@ -58,8 +58,13 @@ struct vptc_ctx {
     RangeDesc* h_ring = nullptr; unsigned int* h_tail = nullptr; // pinned staging, one slot per ring slot
     unsigned int* h_done = nullptr; unsigned int* d_done = nullptr; // mapped pinned completion flags (host pointer / device alias)
     unsigned int n_ranges = 0;       // ranges published so far (absolute range number of the next one)
+    // ---- tile order: full-frame ranges are walked longest-tiles-first once the per-tile job times of this scene are known (prepare_tile_order) ----
+    uint32_t* d_tile_cost = nullptr; uint32_t* d_tile_order = nullptr; size_t order_tiles = 0;
+    SceneDev order_scene{}; bool have_order = false; unsigned long long cost_jobs = 0;
+    bool order_enabled = true;       // VPT_TILE_ORDER=0 in the environment: natural order (row-major tiles, wave-major), as TileProvider hands them out
     // open series of asynchronous launches (vptc_render_device_async / vptc_render_async ... vptc_wait)
     bool series_open = false; int series_launches = 0;
+    bool series_has_plain = false;   // the open series holds a launch that does not read tile lists (see enqueue_render)
     SceneDev series_scene{};         // a call joins the running series only when it renders the same scene
     cudaEvent_t ev_series = nullptr; // recorded before the first launch of the series
     // host-film path: two device films + pinned staging; at most one call's film is still on the device
@@ -170,6 +175,7 @@ struct RangeSpec {
     uint32_t first_wave = 1, wave_stride = 1, tile_row_stride = 1;
     // statistics launches (adaptive rendering): explicit tile list, second-moment plane; run the STATS instantiation of the default kernel
     const uint32_t* tile_list = nullptr; float* sum_y2 = nullptr; bool stats = false;
+    uint32_t* tile_cost = nullptr; // where the kernel adds each finished job's duration (per tile), or null
 };
 
 // Publish a range into the device ring (descriptor first, then the tail, both on the control stream, which runs beside any render kernel
@@ -182,6 +188,7 @@ int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
     d.tile_begin = r.tile_begin; d.tile_count = r.tile_count;
     d.first_wave = r.first_wave; d.wave_stride = r.wave_stride; d.rid = id; d.tile_row_stride = std::max(1u, r.tile_row_stride);
     d.tile_list = r.tile_list; d.sum_y2 = r.sum_y2;
+    d.tile_cost = r.tile_cost; d.n_waves = r.tile_count ? uint32_t(r.n_jobs / r.tile_count) : 0u; d.pad_ = 0;
     ctx->h_tail[slot] = id + 1;
     ctx->h_done[slot] = 0;
     CU(cudaMemcpyAsync(ctx->d_ring + slot, &d, sizeof(RangeDesc), cudaMemcpyHostToDevice, ctx->ctl));
@@ -190,6 +197,36 @@ int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
     CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_ctl, 0)); // this call's own launch starts after its range is visible
     ctx->n_ranges = id + 1;
     *rid = id;
+    return VPTC_OK;
+}
+
+// Longest tiles first. A (tile, wave) job is rendered serially by one lane, so a launch ends with a tail as long as its last jobs; jobs of
+// the expensive tiles (through the core of a cloud) take 100x the time of sky tiles. The kernel records how long each tile's jobs take; as soon
+// as one whole wave of a scene has been timed (and nothing is in flight), the tiles are sorted by that time and every later full-frame range
+// of the scene is walked tile-major in that order: all waves of the expensive tiles start at once, the cheap ones fill the tail. Job ids —
+// and with them every sample — are unchanged; only which lane renders which job when.
+int prepare_tile_order(vptc_ctx* ctx, const SceneDev& sd)
+{
+    const size_t nt = size_t(sd.ntiles);
+    if (ctx->order_tiles != nt || std::memcmp(&ctx->order_scene, &sd, sizeof(SceneDev)) != 0) { // another frame / camera / medium: start over
+        CU(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order);
+        ctx->d_tile_cost = ctx->d_tile_order = nullptr; ctx->order_tiles = 0; ctx->have_order = false; ctx->cost_jobs = 0;
+        CU(cudaMalloc(&ctx->d_tile_cost, nt * 4));
+        CU(cudaMalloc(&ctx->d_tile_order, nt * 4));
+        CU(cudaMemset(ctx->d_tile_cost, 0, nt * 4));
+        ctx->order_tiles = nt;
+        std::memcpy(&ctx->order_scene, &sd, sizeof(SceneDev));
+    }
+    if (!ctx->have_order && ctx->cost_jobs >= nt && !ctx->series_open) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        std::vector<uint32_t> cost(nt), order(nt);
+        CU(cudaMemcpy(cost.data(), ctx->d_tile_cost, nt * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < nt; ++i) order[i] = uint32_t(i);
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
+        CU(cudaMemcpy(ctx->d_tile_order, order.data(), nt * 4, cudaMemcpyHostToDevice));
+        ctx->have_order = true;
+    }
     return VPTC_OK;
 }
 
@@ -210,11 +247,24 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
     int variant = (ctx->variant == 3 && (scene->output_size[0] > 65535 || scene->output_size[1] > 65535 || scene->tile_size[0] > 65535 || scene->tile_size[1] > 65535)) ? 2 : ctx->variant;
     if (variant != 2 && !trace && (r.tile_count != A.scene.ntiles || r.tile_row_stride > 1 || r.stats)) variant = 2; // tile stripes / lists exist in the default kernel only
     const bool stats = r.stats && !trace && !ctx->count;
-    int per_sm = stats ? render_stats_blocks_per_sm() : render_blocks_per_sm(variant, trace, ctx->count);
+    int ord = 0; // tile-order instantiation of the default kernel: 0 none, 1 learning the tiles' costs, 2 ordered (decided below)
+    const bool orderable = variant == 2 && !trace && !r.stats && !ctx->count && ctx->order_enabled && r.tile_begin == 0 && r.tile_count == A.scene.ntiles &&
+                           r.tile_row_stride <= 1 && A.scene.ntiles >= 2 && A.scene.ntiles <= 0xffffffffull && r.n_jobs % r.tile_count == 0;
+    if (orderable) {
+        if (int rc = prepare_tile_order(ctx, A.scene)) return rc;
+        ord = ctx->have_order ? 2 : 1;
+        // A range with a tile list is numbered tile-major, and only the ORD = 2 instantiation reads it that way: lanes of a plain launch of the
+        // same series could carry on into it and number its jobs wave-major. Once a series holds a plain launch, the rest of it stays plain.
+        if (ord == 2 && ctx->series_open && ctx->series_has_plain) ord = 0;
+    }
+    if (variant == 2 && !trace && ord != 2) ctx->series_has_plain = true; // reset when the series closes (wait_all) / a blocking call finishes
+    int per_sm = stats ? render_stats_blocks_per_sm() : ord ? render_ordered_blocks_per_sm(ord) : render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
     if (variant == 2) {
+        if (ord == 2) r.tile_list = ctx->d_tile_order;
+        else if (ord == 1) { r.tile_cost = ctx->d_tile_cost; ctx->cost_jobs += r.n_jobs; }
         unsigned int rid = 0;
         if (int rc = publish_range(ctx, r, &rid)) return rc;
         A.ring = ctx->d_ring; A.ring_tail = ctx->d_tail; A.range_begin = rid; A.host_done = ctx->d_done;
@@ -230,7 +280,7 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
     A.exited = ctx->d_exited; A.exit_limit = unsigned(blocks) * unsigned(per_block) / 2u;
     CU(cudaMemsetAsync(ctx->d_exited, 0, sizeof(unsigned int), ctx->stream)); // same stream: runs between the previous launch and this one
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(stats ? launch_render_stats(A, blocks, ctx->stream) : launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
+    CU(stats ? launch_render_stats(A, blocks, ctx->stream) : ord ? launch_render_ordered(A, ord, blocks, ctx->stream) : launch_render(A, variant, trace, ctx->count, blocks, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     return VPTC_OK;
 }
@@ -307,7 +357,7 @@ int wait_all(vptc_ctx* ctx)
 {
     int rc = collect_pending(ctx);
     if (ctx->series_open) {
-        ctx->series_open = false; ctx->series_launches = 0;
+        ctx->series_open = false; ctx->series_launches = 0; ctx->series_has_plain = false;
         cudaError_t e = cudaEventSynchronize(ctx->ev1);
         if (e == cudaSuccess) e = cudaEventElapsedTime(&ctx->last_ms, ctx->ev_series, ctx->ev1);
         if (e != cudaSuccess && rc == VPTC_OK) rc = fail(ctx, VPTC_ERR_CUDA, std::string("vptc_wait: ") + cudaGetErrorString(e));
@@ -338,6 +388,7 @@ int enqueue_async(vptc_ctx* ctx, const vptc_scene* scene, const vptc_job_range* 
     if (rid) *rid = ~0u; // stays ~0 for the kernels that do not read the ring (variants 0, 1, 3)
     if (r.n_jobs == 0) return VPTC_OK;
     if (!ctx->series_open) {
+        ctx->series_has_plain = false;
         CU(cudaEventRecord(ctx->ev_series, ctx->stream));
         std::memset(&ctx->series_scene, 0, sizeof(SceneDev)); // padding bytes take part in the memcmp above
         ctx->series_scene = sd;
@@ -383,6 +434,7 @@ int stage_volume(vptc_ctx* ctx, const vpt_host::BakedGrid& b, const vpt_host::Ba
     ctx->density = new_density; ctx->temperature = new_temperature;
     ctx->has_temperature = t != nullptr;
     ctx->has_volume = true;
+    ctx->order_tiles = 0; ctx->have_order = false; // another volume: the tiles' costs are learnt afresh
     return VPTC_OK;
 }
 
@@ -438,6 +490,7 @@ int vptc_create(vptc_ctx** out, int device)
     float lambda5[471];
     vpt_host::lambda5_table(lambda5);
     CU(upload_cie_table(vpt_host::cie_table(), lambda5));
+    if (const char* v = std::getenv("VPT_TILE_ORDER")) ctx->order_enabled = std::atoi(v) != 0;
     if (const char* v = std::getenv("VPT_KERNEL_VARIANT")) ctx->variant = std::min(3, std::max(0, std::atoi(v)));
     if (const char* v = std::getenv("VPT_POOL_PARAMS")) // "HOT passes,HOT slots,EVAL slots,SETUP slots" (tuning aid)
         std::sscanf(v, "%d,%d,%d,%d", &ctx->pool_params[0], &ctx->pool_params[1], &ctx->pool_params[2], &ctx->pool_params[3]);
@@ -456,6 +509,7 @@ void vptc_destroy(vptc_ctx* ctx)
     if (ctx->ctl) cudaStreamSynchronize(ctx->ctl);
     cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film[0]); cudaFree(ctx->film[1]);
     cudaFree(ctx->d_ring); cudaFree(ctx->d_tail); cudaFree(ctx->d_exited);
+    cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->pinned_zero) cudaFreeHost(ctx->pinned_zero);
     if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
@@ -501,7 +555,7 @@ int vptc_render_device_range(vptc_ctx* ctx, const vptc_scene* scene, const vptc_
     ctx->last_ms = 0.0f;
     if (int rc = enqueue_async(ctx, scene, range, static_cast<float*>(d_film), nullptr)) return rc;
     if (!ctx->series_open) return VPTC_OK; // empty range
-    ctx->series_open = false; ctx->series_launches = 0;
+    ctx->series_open = false; ctx->series_launches = 0; ctx->series_has_plain = false;
     return finish_render(ctx);
 }
 
