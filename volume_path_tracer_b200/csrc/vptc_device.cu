@@ -59,7 +59,7 @@ struct vptc_ctx {
     unsigned int* h_done = nullptr; unsigned int* d_done = nullptr; // mapped pinned completion flags (host pointer / device alias)
     unsigned int n_ranges = 0;       // ranges published so far (absolute range number of the next one)
     // ---- tile order: full-frame ranges are walked longest-tiles-first once the per-tile job times of this scene are known (prepare_tile_order) ----
-    uint32_t* d_tile_cost = nullptr; uint32_t* d_tile_order = nullptr; size_t order_tiles = 0;
+    uint32_t* d_tile_cost = nullptr; uint32_t* d_tile_order = nullptr; size_t order_tiles = 0, order_capacity = 0;
     SceneDev order_scene{}; bool have_order = false; unsigned long long cost_jobs = 0;
     bool order_enabled = true;       // VPT_TILE_ORDER=0 in the environment: natural order (row-major tiles, wave-major), as TileProvider hands them out
     // open series of asynchronous launches (vptc_render_device_async / vptc_render_async ... vptc_wait)
@@ -210,10 +210,14 @@ int prepare_tile_order(vptc_ctx* ctx, const SceneDev& sd)
     const size_t nt = size_t(sd.ntiles);
     if (ctx->order_tiles != nt || std::memcmp(&ctx->order_scene, &sd, sizeof(SceneDev)) != 0) { // another frame / camera / medium: start over
         CU(cudaStreamSynchronize(ctx->stream));
-        cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order);
-        ctx->d_tile_cost = ctx->d_tile_order = nullptr; ctx->order_tiles = 0; ctx->have_order = false; ctx->cost_jobs = 0;
-        CU(cudaMalloc(&ctx->d_tile_cost, nt * 4));
-        CU(cudaMalloc(&ctx->d_tile_order, nt * 4));
+        ctx->have_order = false; ctx->cost_jobs = 0;
+        if (ctx->order_capacity < nt) { // a moving camera keeps the frame size: the tables are reallocated only when the tile count grows
+            cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order);
+            ctx->d_tile_cost = ctx->d_tile_order = nullptr; ctx->order_tiles = 0; ctx->order_capacity = 0;
+            CU(cudaMalloc(&ctx->d_tile_cost, nt * 4));
+            CU(cudaMalloc(&ctx->d_tile_order, nt * 4));
+            ctx->order_capacity = nt;
+        }
         CU(cudaMemset(ctx->d_tile_cost, 0, nt * 4));
         ctx->order_tiles = nt;
         std::memcpy(&ctx->order_scene, &sd, sizeof(SceneDev));
