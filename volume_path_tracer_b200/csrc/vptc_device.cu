@@ -61,6 +61,9 @@ struct vptc_ctx {
     // ---- tile order: full-frame ranges are walked longest-tiles-first once the per-tile job times of this scene are known (prepare_tile_order) ----
     uint32_t* d_tile_cost = nullptr; uint32_t* d_tile_order = nullptr; size_t order_tiles = 0, order_capacity = 0;
     SceneDev order_scene{}; bool have_order = false; unsigned long long cost_jobs = 0;
+    std::vector<uint32_t> h_order;   // host copy of the sorted tile list: tile STRIPES take their own tiles out of it, in the same order
+    uint32_t* d_stripe_order = nullptr; size_t stripe_capacity = 0;
+    unsigned long long stripe_begin = ~0ull, stripe_count = 0; uint32_t stripe_stride = 0; // which stripe d_stripe_order holds
     bool order_enabled = true;       // VPT_TILE_ORDER=0 in the environment: natural order (row-major tiles, wave-major), as TileProvider hands them out
     // open series of asynchronous launches (vptc_render_device_async / vptc_render_async ... vptc_wait)
     bool series_open = false; int series_launches = 0;
@@ -205,6 +208,7 @@ int publish_range(vptc_ctx* ctx, const RangeSpec& r, unsigned int* rid)
 // as one whole wave of a scene has been timed (and nothing is in flight), the tiles are sorted by that time and every later full-frame range
 // of the scene is walked tile-major in that order: all waves of the expensive tiles start at once, the cheap ones fill the tail. Job ids —
 // and with them every sample — are unchanged; only which lane renders which job when.
+int sort_tiles_if_timed(vptc_ctx* ctx);
 int prepare_tile_order(vptc_ctx* ctx, const SceneDev& sd)
 {
     const size_t nt = size_t(sd.ntiles);
@@ -222,16 +226,55 @@ int prepare_tile_order(vptc_ctx* ctx, const SceneDev& sd)
         ctx->order_tiles = nt;
         std::memcpy(&ctx->order_scene, &sd, sizeof(SceneDev));
     }
-    if (!ctx->have_order && ctx->cost_jobs >= nt && !ctx->series_open) {
+    return sort_tiles_if_timed(ctx);
+}
+// One whole wave of the scene has been timed and nothing is in flight: sort the tiles by the time their jobs took.
+int sort_tiles_if_timed(vptc_ctx* ctx)
+{
+    const size_t nt = ctx->order_tiles;
+    if (!ctx->have_order && nt && ctx->cost_jobs >= nt && !ctx->series_open) {
         CU(cudaStreamSynchronize(ctx->stream));
         std::vector<uint32_t> cost(nt), order(nt);
         CU(cudaMemcpy(cost.data(), ctx->d_tile_cost, nt * 4, cudaMemcpyDeviceToHost));
         for (size_t i = 0; i < nt; ++i) order[i] = uint32_t(i);
         std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
         CU(cudaMemcpy(ctx->d_tile_order, order.data(), nt * 4, cudaMemcpyHostToDevice));
+        ctx->h_order.swap(order);
+        ctx->stripe_begin = ~0ull;
         ctx->have_order = true;
     }
     return VPTC_OK;
+}
+
+// A stripe of tiles (multi-GPU tile sharding: contiguous, or every row_stride-th row of tiles) of a scene whose full-frame order is known:
+// the stripe's own tiles, in that order. One list is cached per context (a rank renders the same stripe call after call); another stripe while
+// a series is in flight keeps the natural order. -> true when ctx->d_stripe_order holds the list for this range.
+bool prepare_stripe_order(vptc_ctx* ctx, const SceneDev& sd, unsigned long long begin, unsigned long long count, uint32_t row_stride)
+{
+    if (ctx->order_tiles != size_t(sd.ntiles) || std::memcmp(&ctx->order_scene, &sd, sizeof(SceneDev)) != 0 || count == 0) return false;
+    if (!ctx->have_order && sort_tiles_if_timed(ctx) != VPTC_OK) return false; // a rank that renders only its stripe after the first full-frame waves
+    if (!ctx->have_order) return false;
+    if (ctx->stripe_begin == begin && ctx->stripe_count == count && ctx->stripe_stride == row_stride) return true;
+    if (ctx->series_open) return false; // the cached list may still be read by ranges in flight
+    const unsigned long long ntx = (unsigned long long)sd.ntx, row0 = begin / ntx, rows = count / ntx;
+    std::vector<uint32_t> list;
+    list.reserve(size_t(count));
+    for (uint32_t t : ctx->h_order) {
+        bool in;
+        if (row_stride <= 1) in = t >= begin && t - begin < count;
+        else { const unsigned long long row = t / ntx; in = row >= row0 && (row - row0) % row_stride == 0 && (row - row0) / row_stride < rows; }
+        if (in) list.push_back(t);
+    }
+    if (list.size() != size_t(count)) return false;
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return false;
+    if (ctx->stripe_capacity < list.size()) {
+        cudaFree(ctx->d_stripe_order); ctx->d_stripe_order = nullptr; ctx->stripe_capacity = 0; ctx->stripe_begin = ~0ull;
+        if (cudaMalloc(&ctx->d_stripe_order, list.size() * 4) != cudaSuccess) { cudaGetLastError(); return false; }
+        ctx->stripe_capacity = list.size();
+    }
+    if (cudaMemcpy(ctx->d_stripe_order, list.data(), list.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); ctx->stripe_begin = ~0ull; return false; }
+    ctx->stripe_begin = begin; ctx->stripe_count = count; ctx->stripe_stride = row_stride;
+    return true;
 }
 
 // Enqueue the megakernel for one range on the render stream; does not wait. `full_grid`: a launch that later calls may join needs every SM.
@@ -261,13 +304,18 @@ int enqueue_render(vptc_ctx* ctx, const vptc_scene* scene, RenderArgs& A, RangeS
         // same series could carry on into it and number its jobs wave-major. Once a series holds a plain launch, the rest of it stays plain.
         if (ord == 2 && ctx->series_open && ctx->series_has_plain) ord = 0;
     }
+    // a stripe of a scene whose order is known: its own tiles, longest first (no learning on stripes: the costs come from full-frame calls)
+    const bool stripe = variant == 2 && !trace && !r.stats && !ctx->count && ctx->order_enabled && !orderable && r.tile_count > 1 && r.tile_count < A.scene.ntiles &&
+                        A.scene.ntiles <= 0xffffffffull && r.n_jobs % r.tile_count == 0 && !(ctx->series_open && ctx->series_has_plain);
+    const uint32_t* stripe_list = nullptr;
+    if (stripe && prepare_stripe_order(ctx, A.scene, r.tile_begin, r.tile_count, std::max(1u, r.tile_row_stride))) { ord = 2; stripe_list = ctx->d_stripe_order; }
     if (variant == 2 && !trace && ord != 2) ctx->series_has_plain = true; // reset when the series closes (wait_all) / a blocking call finishes
     int per_sm = stats ? render_stats_blocks_per_sm() : ord ? render_ordered_blocks_per_sm(ord) : render_blocks_per_sm(variant, trace, ctx->count);
     if (const char* v = std::getenv("VPT_MAX_BLOCKS_PER_SM")) per_sm = std::min(per_sm, std::max(1, std::atoi(v))); // occupancy experiments
     if (per_sm <= 0) return fail(ctx, VPTC_ERR_CUDA, "render kernel cannot be resident on this device (occupancy query returned 0)");
     if (ctx->count) CU(cudaMemsetAsync(ctx->counters, 0, sizeof(CountersDev), ctx->stream));
     if (variant == 2) {
-        if (ord == 2) r.tile_list = ctx->d_tile_order;
+        if (ord == 2) r.tile_list = stripe_list ? stripe_list : ctx->d_tile_order;
         else if (ord == 1) { r.tile_cost = ctx->d_tile_cost; ctx->cost_jobs += r.n_jobs; }
         unsigned int rid = 0;
         if (int rc = publish_range(ctx, r, &rid)) return rc;
@@ -513,7 +561,7 @@ void vptc_destroy(vptc_ctx* ctx)
     if (ctx->ctl) cudaStreamSynchronize(ctx->ctl);
     cudaFree(ctx->bb_table); cudaFree(ctx->queue); cudaFree(ctx->counters); cudaFree(ctx->film[0]); cudaFree(ctx->film[1]);
     cudaFree(ctx->d_ring); cudaFree(ctx->d_tail); cudaFree(ctx->d_exited);
-    cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order);
+    cudaFree(ctx->d_tile_cost); cudaFree(ctx->d_tile_order); cudaFree(ctx->d_stripe_order);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->pinned_zero) cudaFreeHost(ctx->pinned_zero);
     if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
