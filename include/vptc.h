@@ -108,7 +108,10 @@ VPTC_API int vptc_set_volume(vptc_ctx* ctx, const void* density_grid, size_t den
  * first_wave .. first_wave + n_waves - 1 (1-based, tile_provider.cpp:30); job ids are
  * jid = (wave-1)*ntiles + tile exactly as TileProvider::next() hands them out.  ADDS
  * (imaging_ratio*L, 1) per pixel-sample into the caller-owned host film, H x W row-major float[4]
- * (worker.cpp:203-204, image.hpp:59).  Host<->device copies are inside the call. */
+ * (worker.cpp:203-204, image.hpp:59).  Host<->device copies are inside the call.
+ * WHICH lane renders a job WHEN is the library's business: after the first wave(s) of a scene it renders full-frame calls (and tile stripes)
+ * longest-tiles-first, tile-major, from per-tile job times it has measured.  The job ids, hence every sample, are the
+ * reference's; films differ from call to call by fp32 add order only.  VPT_TILE_ORDER=0 in the environment keeps TileProvider's order. */
 VPTC_API int vptc_render(vptc_ctx* ctx, const vptc_scene* scene, uint32_t first_wave, uint32_t n_waves,
                          float* film_xyzw);
 
